@@ -1,0 +1,178 @@
+"""Generate tests/golden/* by running the REAL reference (/root/reference, importable only in
+the build container) on the seeded weight recipe, and pin the oracle restatement against it.
+
+    python scripts/make_goldens.py
+
+What it writes (all small; inputs are re-derivable from seeds so only outputs are stored):
+  tests/golden/state_dict_keys_{vits,vitl}.json   name -> shape of the reference state dict
+  tests/golden/forward_*.npz                      reference fp32 CPU forward outputs (+ taps)
+  tests/golden/driver_*.npz                       reference infer_video_depth output (fp32, CPU)
+  tests/golden/window_index_map.json              source-frame index map for several lengths
+  tests/golden/MANIFEST.json                      max |oracle - reference| per case, versions
+"""
+import json
+import os
+import sys
+import types
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, "/root/reference")
+
+ed = types.ModuleType("easydict")  # the only missing import on the path (dpt_temporal.py:19)
+
+
+class EasyDict(dict):
+    __getattr__ = dict.__getitem__
+    __setattr__ = dict.__setitem__
+
+
+ed.EasyDict = EasyDict
+sys.modules["easydict"] = ed
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from oracle import driver as odrv  # noqa: E402
+from oracle import model as omodel  # noqa: E402
+from oracle.weights import MODEL_CONFIGS, make_state_dict, param_spec  # noqa: E402
+from oracle.inputs import synthetic_clip, synthetic_video  # noqa: E402
+
+from video_depth_anything.video_depth import VideoDepthAnything  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+os.makedirs(GOLD, exist_ok=True)
+torch.set_num_threads(os.cpu_count())
+manifest = {"torch": torch.__version__, "numpy": np.__version__, "cases": {}}
+
+
+def ref_model(encoder, num_frames=32):
+    m = VideoDepthAnything(**MODEL_CONFIGS[encoder], num_frames=num_frames)
+    sd = make_state_dict(encoder, seed=0, num_frames=num_frames)
+    ref_sd = m.state_dict()
+    spec = param_spec(encoder, num_frames)
+    assert list(ref_sd.keys()) == list(spec.keys()), "param_spec order/keys differ from the reference"
+    for k, v in ref_sd.items():
+        assert tuple(v.shape) == tuple(spec[k]), (k, v.shape, spec[k])
+    with open(os.path.join(GOLD, f"state_dict_keys_{encoder}.json"), "w") as f:
+        json.dump({k: list(v) for k, v in spec.items()}, f, indent=0)
+    # the recipe's pe buffer must equal the reference's own buffer
+    for k, v in ref_sd.items():
+        if k.endswith(".pe"):
+            assert torch.equal(v, sd[k]), k
+    m.load_state_dict(sd, strict=True)
+    return m.eval(), sd
+
+
+def hook_taps(m):
+    got = {}
+    hs = []
+    for i in range(4):
+        hs.append(m.head.motion_modules[i].register_forward_hook(
+            lambda mod, a, out, i=i: got.__setitem__(f"mm{i}", out.detach())))
+    return got, hs
+
+
+def forward_case(name, encoder, T, H, W, seed, sub=1, skip_tmp_block=False):
+    m, sd = ref_model(encoder)
+    x = synthetic_clip(1, T, H, W, seed)
+    got, hs = hook_taps(m)
+    with torch.no_grad():
+        ref = m(x, skip_tmp_block) if skip_tmp_block else m(x)
+        feats = m.pretrained.get_intermediate_layers(x.flatten(0, 1), m.intermediate_layer_idx[encoder],
+                                                     return_class_token=True)
+    for h in hs:
+        h.remove()
+    col = {}
+    with torch.no_grad():
+        ora = omodel.forward(sd, x, encoder, skip_tmp_block, collect=col)
+    err = float((ora - ref).abs().max())
+    tap_err = max(float((col[f"tap{i}"] - feats[i][0]).abs().max()) for i in range(4))
+    # motion-module hook outputs are [B,C,T,h,w]; oracle keeps [(b f),C,h,w]
+    mm_err = 0.0
+    for i, key in ((0, "mm0"), (1, "mm1")):
+        r = got[key].permute(0, 2, 1, 3, 4).flatten(0, 1)
+        mm_err = max(mm_err, float((col[key] - r).abs().max()))
+    print(f"{name}: oracle-vs-reference max|d| depth {err:.3e} taps {tap_err:.3e} mm {mm_err:.3e}; "
+          f"depth range [{float(ref.min()):.4f}, {float(ref.max()):.4f}] zeros {(ref == 0).float().mean():.4f}")
+    assert err <= 1e-5 * float(ref.abs().max()) + 1e-6, "oracle restatement diverges from the reference"
+    out = {"depth": ref[0, :, ::sub, ::sub].numpy().astype(np.float32),
+           "meta": np.array([T, H, W, seed, sub, int(skip_tmp_block)], dtype=np.int64)}
+    for i in range(4):
+        t = feats[i][0]
+        out[f"tap{i}"] = t[:, :: max(1, t.shape[1] // 64), :: max(1, t.shape[2] // 48)].numpy().astype(np.float32)
+    np.savez_compressed(os.path.join(GOLD, f"forward_{name}.npz"), **out)
+    manifest["cases"][f"forward_{name}"] = {"encoder": encoder, "T": T, "H": H, "W": W, "seed": seed, "sub": sub,
+                                            "oracle_vs_reference_max_abs": err,
+                                            "depth_min": float(ref.min()), "depth_max": float(ref.max())}
+
+
+def driver_case(name, encoder, n, fh, fw, input_size, seed):
+    m, sd = ref_model(encoder)
+    frames = synthetic_video(n, fh, fw, seed)
+    ref, fps = m.infer_video_depth(frames, 24, input_size=input_size, device="cpu", fp32=True)
+    ora, _, raw, st = odrv.infer_video_depth(frames, 24, lambda x: omodel.forward(sd, x, encoder),
+                                             input_size=input_size, device="cpu", fp32=True, return_raw=True)
+    err = float(np.abs(ora - ref).max())
+    print(f"{name}: driver oracle-vs-reference max|d| {err:.3e}; out {ref.shape} range "
+          f"[{ref.min():.4f},{ref.max():.4f}] scale/shift {st[:3]}")
+    assert ref.shape == (n, fh, fw) and fps == 24
+    assert err <= 1e-5 * float(np.abs(ref).max()) + 1e-6
+    np.savez_compressed(os.path.join(GOLD, f"driver_{name}.npz"), depth=ref.astype(np.float32),
+                        scale_shift=np.asarray(st, dtype=np.float64),
+                        meta=np.array([n, fh, fw, input_size, seed], dtype=np.int64))
+    manifest["cases"][f"driver_{name}"] = {"encoder": encoder, "n": n, "fh": fh, "fw": fw,
+                                           "input_size": input_size, "seed": seed,
+                                           "oracle_vs_reference_max_abs": err}
+
+
+def preprocess_case():
+    """Reference transform pipeline (transform.py) vs oracle.preprocess_frame on odd sizes."""
+    import cv2
+    from torchvision.transforms import Compose
+    from video_depth_anything.util.transform import NormalizeImage, PrepareForNet, Resize
+    res = {}
+    for (fh, fw, isz) in [(48, 64, 56), (72, 128, 70), (60, 60, 56), (37, 111, 56)]:
+        isz_eff = odrv.effective_input_size(fh, fw, isz)
+        tr = Compose([Resize(width=isz_eff, height=isz_eff, resize_target=False, keep_aspect_ratio=True,
+                             ensure_multiple_of=14, resize_method="lower_bound",
+                             image_interpolation_method=cv2.INTER_CUBIC),
+                      NormalizeImage(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225]), PrepareForNet()])
+        fr = synthetic_video(1, fh, fw, 3)[0]
+        ref = tr({"image": fr.astype(np.float32) / 255.0})["image"]
+        ora = odrv.preprocess_frame(fr, isz_eff)
+        assert ref.shape == ora.shape and np.array_equal(ref, ora), (fh, fw, isz)
+        res[f"{fh}x{fw}@{isz}"] = [int(ref.shape[1]), int(ref.shape[2]), float(ref.sum()), float(np.abs(ref).max())]
+    return res
+
+
+if __name__ == "__main__":
+    maps = {str(n): odrv.window_index_map(n).tolist() for n in (1, 5, 22, 23, 32, 44, 45, 70, 100)}
+    # pin the index map against the reference driver by feeding frames whose value encodes their index
+    for n in (1, 23, 70):
+        class Probe(VideoDepthAnything):
+            seen = []
+
+            def forward(self, x, skip_tmp_block=False):
+                # channel 0 mean of each frame encodes the source index (frames are constant images)
+                v = x[0, :, 0, 0, 0] * 0.229 + 0.485
+                Probe.seen.append([int(round(float(t) * 255.0)) for t in v])
+                return torch.zeros(x.shape[0], x.shape[1], x.shape[3], x.shape[4])
+        Probe.seen = []
+        pm = Probe(**MODEL_CONFIGS["vits"])
+        fr = np.stack([np.full((28, 28, 3), i, np.uint8) for i in range(n)])
+        pm.infer_video_depth(fr, 24, input_size=28, device="cpu", fp32=True)
+        assert Probe.seen == maps[str(n)], (n, Probe.seen, maps[str(n)])
+    with open(os.path.join(GOLD, "window_index_map.json"), "w") as f:
+        json.dump(maps, f)
+    manifest["preprocess"] = preprocess_case()
+
+    forward_case("vits_T4_42x56", "vits", 4, 42, 56, seed=1)
+    forward_case("vits_T32_28x28_skip", "vits", 32, 28, 28, seed=2, skip_tmp_block=True)
+    forward_case("vits_T2_518x518", "vits", 2, 518, 518, seed=3, sub=7)
+    forward_case("vitl_T3_28x42", "vitl", 3, 28, 42, seed=4)
+    driver_case("vits_n50_48x64", "vits", 50, 48, 64, 56, seed=5)
+    driver_case("vits_n23_40x90", "vits", 23, 40, 90, 56, seed=6)  # ratio > 1.78 branch
+    with open(os.path.join(GOLD, "MANIFEST.json"), "w") as f:
+        json.dump(manifest, f, indent=1)
+    print("goldens written to", GOLD)
