@@ -1,0 +1,187 @@
+/*
+ * libvda_sm100a.so -- C ABI of the B200-native Video-Depth-Anything inference hot path.
+ *
+ * The reference (FriedFeid/Video-Depth-Anything) is pure Python/PyTorch and has no FFI of its own
+ * (SURVEY.md section 8b): every entry point below replaces the library kernel(s) that PyTorch eager
+ * dispatches for the cited reference lines.  Conventions:
+ *   - extern "C", plain pointers and sizes; no torch / C++ types in any signature;
+ *   - every pointer is a DEVICE pointer owned by the caller unless the name says `host`;
+ *   - every launcher takes a cudaStream_t (as void*) and is asynchronous; no hidden allocation, no hidden sync;
+ *   - return value: 0 = ok, otherwise a cudaError_t (>0) or a negative library code; vda_last_error() gives text;
+ *   - built only for sm_100a; there is no CPU path and no other architecture.
+ *
+ * Activation layout everywhere: token-major / channels-last.  A feature map of `frames` images of h x w
+ * pixels and C channels is a row-major matrix [frames*h*w, C] ("dense"), or, when it feeds a 3x3
+ * convolution, [frames*(h+2)*(w+2), C] with a zero one-pixel border per image ("padded").  In padded
+ * form a 3x3 tap is a constant row offset, so convolutions are GEMMs with a 9-step K loop.
+ */
+#ifndef VDA_H_
+#define VDA_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VDA_VERSION 1
+
+typedef void* vda_stream_t; /* cudaStream_t */
+
+enum vda_dtype { VDA_F32 = 0, VDA_BF16 = 1 };
+
+/* How a row index m of the GEMM's M space maps to a row of an output / residual matrix.
+ * (b, y, x) is the pixel of m in a grid of gh x gw pixels per frame (dense M space: m = (b*gh+y)*gw+x;
+ * padded M space: m = (b*(gh+2)+y+1)*(gw+2)+x+1, border rows produce no output). */
+enum vda_rowmap {
+  VDA_MAP_SAME = 0,    /* row = m                                                                  */
+  VDA_MAP_DENSE = 1,   /* row = (b*gh + y)*gw + x                                                  */
+  VDA_MAP_PADDED = 2,  /* row = (b*(gh+2) + y+1)*(gw+2) + x+1                                      */
+  VDA_MAP_STRIDE2 = 3, /* only even y,x: row = (b*gh2 + y/2)*gw2 + x/2, gh2=(gh+1)/2, gw2=(gw+1)/2 */
+  VDA_MAP_TOKENS = 4,  /* row = m + m/(gh*gw) + 1  (one class-token row precedes each frame)       */
+  VDA_MAP_CONVT = 5    /* conv-transpose k=s: row = padded index of (b, y*k+ky, x*k+kx) in a
+                          (gh*k) x (gw*k) grid; (ky,kx) come from the column index                 */
+};
+
+enum vda_act { VDA_ACT_NONE = 0, VDA_ACT_GELU = 1, VDA_ACT_GEGLU = 2, VDA_ACT_RELU = 3 };
+
+/*
+ * One dense contraction with a fused epilogue:  acc[m,n] = sum_{t<taps} sum_{k<K} A[m + off(t), k] * B[n, (s*taps+t)*K + k]
+ * (summed over s < ksplit), followed by the epilogue described field by field below.
+ *
+ * Replaces, in the reference:
+ *   nn.Linear  : dinov2_layers/attention.py:44-46,57-60 (qkv, proj), dinov2_layers/mlp.py:30-32,35-41 (fc1+GELU, fc2),
+ *                layer_scale.py:27-28 + block.py:105-106 (LayerScale + residual, fused as `resid`),
+ *                motion_module/motion_module.py:90,106,119,127 (proj_in/out), motion_module/attention.py:81-90 (to_q/k/v, to_out),
+ *                attention.py:374,382-384 (GEGLU), :333 (ff out)
+ *   nn.Conv2d  : patch_embed.py:66,76 (k14 s14 via vda_im2col_patch), dpt.py:50-58 (projects 1x1), :83-88 (3x3 s2),
+ *                util/blocks.py:20-33 (layerN_rn), :56-62,78-91 (ResidualConvUnit), :123-125,160 (out_conv),
+ *                dpt.py:117-124 (output_conv1, output_conv2 incl. the fused ReLU -> 1x1 -> ReLU tail)
+ *   nn.ConvTranspose2d k=s : dpt.py:61-72 (resize_layers[0], [1])
+ */
+typedef struct vda_gemm_desc {
+  /* ---- operands ---- */
+  const void* A;     /* [rowsA, K] row-major, leading dimension lda (elements)                       */
+  const void* B;     /* [N, ksplit*taps*K] row-major (K-major packed weights), leading dimension ldb */
+  int64_t lda, ldb;
+  int64_t rowsA;     /* rows of A that exist; reads outside [0,rowsA) yield 0                        */
+  int32_t a_dtype;   /* vda_dtype of A                                                               */
+  int32_t b_dtype;   /* vda_dtype of B                                                               */
+  int32_t M, N, K;   /* K = contraction length per tap                                               */
+  int32_t taps;      /* 1 = plain GEMM; 9 = 3x3 conv over a padded M space, off(t) = (t/3-1)*(gw+2) + (t%3-1) */
+  int32_t ksplit;    /* 1, or 2 when B carries a (hi, lo) bf16 split of fp32 weights along K         */
+  /* ---- geometry of the M space ---- */
+  int32_t gb, gh, gw; /* frames, dense grid height / width (0,0,0 when no map needs them)             */
+  int32_t m_padded;  /* 1: m runs over the padded (gh+2)x(gw+2) grid                                 */
+  /* ---- epilogue: v = acc + bias[n]; v = R(v); v = act(v) ... (R = round-to-bf16 when round_bf16) ---- */
+  const float* bias; /* [N] (conv-transpose: [ct_cout], indexed n % ct_cout) or NULL                  */
+  int32_t act;       /* vda_act; GEGLU: B rows are packed in groups of 64 = 32 value rows + 32 gate rows,
+                        output column count is N/2                                                   */
+  int32_t round_bf16; /* 1: reproduce the autocast rounding points; 0: pure fp32 arithmetic            */
+  int32_t out_dtype; /* storage type of out / out_relu / res / res2                                  */
+  void* out;         /* primary output (may be NULL when only `resid` or `head_out` is produced)     */
+  void* out_relu;    /* optional second copy, relu(v)                                                */
+  int64_t ldo;
+  int32_t out_map;   /* vda_rowmap                                                                   */
+  int32_t ct_k;      /* VDA_MAP_CONVT: kernel = stride; N = ct_k*ct_k*ct_cout, n = (ky*ct_k+kx)*ct_cout+co */
+  int32_t ct_cout;
+  const void* res;   /* optional: v = R(v + res[row, n])                                             */
+  const void* res2;  /* optional: v = R(v + res2[row, n])                                            */
+  int64_t ldres;
+  int32_t res_map;
+  /* fp32 residual stream (encoder): resid[row, n] = resid[row, n] + gamma[n]*v,
+     or with resid_assign: resid[row, n] = v + pos[(row % pos_rows), n]  (patch embed + pos-embed)    */
+  float* resid;
+  const float* gamma;
+  const float* pos;
+  int64_t ldresid;
+  int32_t resid_map;
+  int32_t resid_assign;
+  int32_t pos_rows;
+  /* fused output tail (dpt.py:119-123): d = relu(sum_n relu(acc+bias)[n]*head_w[n] + head_b); head_out[row] = R(d) */
+  const float* head_w;
+  void* head_out;    /* [rows] of out_dtype                                                          */
+  float head_b;
+  /* ---- execution ---- */
+  int32_t use_tc;    /* 1: tcgen05/TMEM/TMA kernel (bf16 operands); 0: SIMT fp32-accumulate kernel   */
+  void* workspace;   /* SIMT path only: >= M*N*4 bytes of scratch                                    */
+  int64_t workspace_bytes;
+} vda_gemm_desc;
+
+const char* vda_last_error(void);
+int vda_version(void);
+/* 0 when device `dev` is an sm_100 part and the library can run; fills sm_count when non-NULL. */
+int vda_device_check(int dev, int* sm_count);
+
+int vda_gemm(const vda_gemm_desc* d, vda_stream_t stream);
+
+/* LayerNorm over the last dim D of x[rows, D] (dinov2.py:95 eps 1e-6; block.py:83-87; dinov2.py:309-310;
+ * motion_module.py:162-170,175-183 eps 1e-5).  y = R((x-mean)*rstd*w + b (+ pe[(r / pe_group) % pe_T, :])).
+ * skip_first/group_rows: drop row 0 of every group of `group_rows` rows from the output (class token,
+ * dinov2.py:312) -- the output then has rows - rows/group_rows rows. */
+int vda_layernorm(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, const float* w, const float* b,
+                  float eps, int64_t rows, int32_t D, int32_t group_rows, int32_t skip_first,
+                  const float* pe, int32_t pe_group, int32_t pe_T, vda_stream_t stream);
+
+/* GroupNorm(groups, C, eps) per frame over dense tokens x[frames, hw, C] (motion_module.py:89,116) -> y tokens.
+ * stats: scratch of frames*groups*2 doubles. */
+int vda_groupnorm_tokens(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, const float* w, const float* b,
+                         float eps, int32_t frames, int32_t hw, int32_t C, int32_t groups, double* stats,
+                         vda_stream_t stream);
+
+/* Encoder self-attention (dinov2_layers/attention.py:49-59): qkv[frames*ntok, 3*heads*64] -> o[frames*ntok, heads*64];
+ * softmax(0.125 * q k^T) v per (frame, head).  head_dim is 64 for every DINOv2 size. */
+int vda_attention(const void* qkv, void* o, int32_t dtype, int32_t frames, int32_t ntok, int32_t heads,
+                  int32_t round_bf16, int32_t use_tc, vda_stream_t stream);
+
+/* Temporal attention over the frame axis (motion_module.py:253,317-322; motion_module/attention.py:182-211):
+ * qkv[(b*T + t)*hw + p, 3*C] -> o[(b*T+t)*hw + p, C]; `heads` heads of C/heads; one problem per (b, p, head). */
+int vda_temporal_attention(const void* qkv, void* o, int32_t dtype, int32_t batch, int32_t T, int32_t hw, int32_t C,
+                           int32_t heads, int32_t round_bf16, vda_stream_t stream);
+
+/* Bilinear resize, align_corners=True (blocks.py:156-158, dpt_temporal.py:92-94), channels-last. */
+int vda_bilinear(const void* in, void* out, int32_t dtype, int32_t frames, int32_t ih, int32_t iw, int32_t in_padded,
+                 int32_t oh, int32_t ow, int32_t out_padded, int32_t C, vda_stream_t stream);
+
+/* Patch-embed im2col (patch_embed.py:76): x[frames,3,H,W] f32 -> A[frames*(H/14)*(W/14), kpad] (k = c*196+i*14+j; pad = 0). */
+int vda_im2col_patch(const float* x, void* A, int32_t a_dtype, int32_t frames, int32_t H, int32_t W, int32_t kpad,
+                     vda_stream_t stream);
+
+/* Class-token rows of the residual stream (dinov2.py:220-221): resid[f*ntok, :] = cls + pos[0, :]. */
+int vda_cls_rows(float* resid, const float* cls, const float* pos, int32_t frames, int32_t ntok, int32_t D,
+                 vda_stream_t stream);
+
+/* Bicubic (a=-0.75, align_corners=False, explicit scale) resample of the 37x37 position grid (dinov2.py:179-210). */
+int vda_pos_embed_bicubic(const float* pos, float* out, int32_t D, int32_t src, int32_t oh, int32_t ow,
+                          double scale_h, double scale_w, vda_stream_t stream);
+
+/* ---- sliding-window driver kernels (video_depth.py:329-417, util/transform.py, utils/util.py) ---- */
+
+/* uint8 HWC frame -> /255 -> cv2.INTER_CUBIC resize to (oh, ow) -> (x-mean)/std -> planar f32 [3, oh, ow]
+ * (transform.py:109-158, video_depth.py:361), `n` frames at once. */
+int vda_preprocess_u8(const uint8_t* frames, float* out, int32_t n, int32_t fh, int32_t fw, int32_t oh, int32_t ow,
+                      vda_stream_t stream);
+
+/* depth[n, ih, iw] (dtype) -> f32 [n, oh, ow], bilinear align_corners=True on the f32-converted values
+ * (video_depth.py:370-371). */
+int vda_resize_depth(const void* in, int32_t dtype, float* out, int32_t n, int32_t ih, int32_t iw, int32_t oh,
+                     int32_t ow, vda_stream_t stream);
+
+/* Scale/shift least squares (utils/util.py:40-62 with an all-ones mask):
+ * st[0..1] = (scale, shift) minimising |scale*pred + shift - target|^2; the five sums are accumulated in f64 in
+ * scratch[0..4].  phase bit 0: zero the scratch first; bit 1: solve into st after accumulating.  The reference fits
+ * over two frames (video_depth.py:390-395): call once per frame pair with phase 1 then 2. */
+int vda_scale_shift(const float* pred, const float* target, int64_t count, double* scratch, float* st, int32_t phase,
+                    vda_stream_t stream);
+
+/* out = max(in*st[0] + st[1], 0) over count elements (video_depth.py:399-412). */
+int vda_scale_clamp(const float* in, float* out, const float* st, int64_t count, vda_stream_t stream);
+
+/* 8-frame linear cross-fade (utils/util.py:65-74, video_depth.py:397-402):
+ * inout[i] = inout[i]*(1-w_i) + max(post[i]*st[0]+st[1], 0)*w_i, w = i/(n-1). */
+int vda_blend(float* inout, const float* post, const float* st, int32_t n, int64_t frame_elems, vda_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VDA_H_ */

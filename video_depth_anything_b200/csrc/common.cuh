@@ -1,0 +1,101 @@
+// Shared device/host helpers for libvda_sm100a.  sm_100a only.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/vda.h"
+
+typedef __nv_bfloat16 bf16;
+
+// ---------------------------------------------------------------- error plumbing
+void vda_set_error(const char* fmt, ...);
+#define VDA_CHECK_ARG(cond, ...)        \
+  do {                                  \
+    if (!(cond)) {                      \
+      vda_set_error(__VA_ARGS__);       \
+      return -1;                        \
+    }                                   \
+  } while (0)
+#define VDA_CUDA_LAUNCH_CHECK(name)                                             \
+  do {                                                                          \
+    cudaError_t e__ = cudaGetLastError();                                       \
+    if (e__ != cudaSuccess) {                                                   \
+      vda_set_error("%s launch failed: %s", name, cudaGetErrorString(e__));     \
+      return (int)e__;                                                          \
+    }                                                                           \
+  } while (0)
+
+// ---------------------------------------------------------------- numeric helpers
+// Round an fp32 value to the nearest bf16 (RNE) and come back: the "rounding point" of autocast.
+__device__ __forceinline__ float round_bf16(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+template <bool RB>
+__device__ __forceinline__ float R(float v) {
+  if constexpr (RB) return round_bf16(v);
+  else return v;
+}
+// exact-erf GELU, the nn.GELU() / F.gelu default (dinov2.py:61, motion_module/attention.py:378)
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<bf16>(bf16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f32<bf16>(float v) { return __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&p);
+}
+__device__ __forceinline__ float bf16lo_to_f32(uint32_t p) { return __uint_as_float(p << 16); }
+__device__ __forceinline__ float bf16hi_to_f32(uint32_t p) { return __uint_as_float(p & 0xffff0000u); }
+
+// load / store `n` (<=8, multiple handled by caller) consecutive elements as fp32
+template <typename T> struct Vec8;
+template <> struct Vec8<float> {
+  static __device__ __forceinline__ void load(const float* p, float* v) {
+    float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+  static __device__ __forceinline__ void store(float* p, const float* v) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+};
+template <> struct Vec8<bf16> {
+  static __device__ __forceinline__ void load(const bf16* p, float* v) {
+    uint4 a = *reinterpret_cast<const uint4*>(p);
+    v[0] = bf16lo_to_f32(a.x); v[1] = bf16hi_to_f32(a.x); v[2] = bf16lo_to_f32(a.y); v[3] = bf16hi_to_f32(a.y);
+    v[4] = bf16lo_to_f32(a.z); v[5] = bf16hi_to_f32(a.z); v[6] = bf16lo_to_f32(a.w); v[7] = bf16hi_to_f32(a.w);
+  }
+  static __device__ __forceinline__ void store(bf16* p, const float* v) {
+    uint4 a;
+    a.x = pack_bf16x2(v[0], v[1]); a.y = pack_bf16x2(v[2], v[3]);
+    a.z = pack_bf16x2(v[4], v[5]); a.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(p) = a;
+  }
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+static inline int vda_sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}

@@ -1,0 +1,208 @@
+// Kernels of the sliding-window driver (video_depth.py:329-417): frame pre-processing, the resize of the depth maps
+// back to frame size, the scale/shift least squares, scale+clamp and the 8-frame cross-fade.  All HBM-bound.
+#include "common.cuh"
+
+namespace {
+
+// cv2.resize(INTER_CUBIC) on float32 HWC (transform.py:113): src = (dst+0.5)*scale-0.5, taps floor-1..+2 with replicate
+// border, coefficients with A=-0.75 and c3 = 1-c0-c1-c2, horizontal pass then vertical pass.
+__device__ __forceinline__ void cv_cubic_coeffs(float x, float* c) {
+  const float A = -0.75f;
+  c[0] = ((A * (x + 1) - 5 * A) * (x + 1) + 8 * A) * (x + 1) - 4 * A;
+  c[1] = ((A + 2) * x - (A + 3)) * x * x + 1;
+  c[2] = ((A + 2) * (1 - x) - (A + 3)) * (1 - x) * (1 - x) + 1;
+  c[3] = 1.f - c[0] - c[1] - c[2];
+}
+
+__global__ void __launch_bounds__(256) preprocess_kernel(const uint8_t* __restrict__ frames, float* __restrict__ out, int fh,
+                                                        int fw, int oh, int ow, double sy, double sx, long long total) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int x = (int)(idx % ow);
+  const int y = (int)((idx / ow) % oh);
+  const int f = (int)(idx / ((long long)ow * oh));
+  const uint8_t* img = frames + (long long)f * fh * fw * 3;
+  float v[3];
+  if (oh == fh && ow == fw) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) v[c] = (float)img[((long long)y * fw + x) * 3 + c] / 255.0f;
+  } else {
+    float fy = (float)((y + 0.5) * sy - 0.5), fx = (float)((x + 0.5) * sx - 0.5);
+    const int iy = (int)floorf(fy), ix = (int)floorf(fx);
+    fy -= iy;
+    fx -= ix;
+    float cy[4], cx[4];
+    cv_cubic_coeffs(fy, cy);
+    cv_cubic_coeffs(fx, cx);
+    v[0] = v[1] = v[2] = 0.f;
+    float rows[4][3];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int yy = min(max(iy - 1 + i, 0), fh - 1);
+      float p[4][3];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int xx = min(max(ix - 1 + j, 0), fw - 1);
+        const uint8_t* px = img + ((long long)yy * fw + xx) * 3;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) p[j][c] = (float)px[c] / 255.0f;
+      }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) rows[i][c] = p[0][c] * cx[0] + p[1][c] * cx[1] + p[2][c] * cx[2] + p[3][c] * cx[3];
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) v[c] = rows[0][c] * cy[0] + rows[1][c] * cy[1] + rows[2][c] * cy[2] + rows[3][c] * cy[3];
+  }
+  // NormalizeImage promotes to float64 (python-list mean/std), PrepareForNet casts back to f32 (transform.py:133-148)
+  const double mean[3] = {0.485, 0.456, 0.406}, stdv[3] = {0.229, 0.224, 0.225};
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+    out[(((long long)f * 3 + c) * oh + y) * ow + x] = (float)(((double)v[c] - mean[c]) / stdv[c]);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) resize_depth_kernel(const T* __restrict__ in, float* __restrict__ out, int ih, int iw,
+                                                          int oh, int ow, float rh, float rw, long long total) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int ox = (int)(idx % ow);
+  const int oy = (int)((idx / ow) % oh);
+  const int f = (int)(idx / ((long long)ow * oh));
+  const float h1r = rh * oy;
+  const int h1 = (int)h1r, h1p = (h1 < ih - 1) ? 1 : 0;
+  const float h1l = h1r - h1, h0l = 1.f - h1l;
+  const float w1r = rw * ox;
+  const int w1 = (int)w1r, w1p = (w1 < iw - 1) ? 1 : 0;
+  const float w1l = w1r - w1, w0l = 1.f - w1l;
+  const T* p = in + ((long long)f * ih + h1) * iw + w1;
+  const float a = to_f32<T>(p[0]), b = to_f32<T>(p[w1p]), c = to_f32<T>(p[(long long)h1p * iw]),
+              d = to_f32<T>(p[(long long)h1p * iw + w1p]);
+  out[idx] = h0l * (w0l * a + w1l * b) + h1l * (w0l * c + w1l * d);
+}
+
+__global__ void __launch_bounds__(256) ls_sums_kernel(const float* __restrict__ pred, const float* __restrict__ tgt,
+                                                     long long count, double* __restrict__ sums) {
+  double s[4] = {0, 0, 0, 0};  // sum p*p, sum p, sum p*t, sum t
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+    const double p = pred[i], t = tgt[i];
+    s[0] += p * p; s[1] += p; s[2] += p * t; s[3] += t;
+  }
+  __shared__ double sh[4][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
+    if (lane == 0) sh[k][warp] = s[k];
+  }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    double t = 0;
+    for (int w = 0; w < 8; ++w) t += sh[threadIdx.x][w];
+    atomicAdd(&sums[threadIdx.x], t);
+  }
+  if (threadIdx.x == 0 && blockIdx.x == 0) atomicAdd(&sums[4], (double)count);
+}
+
+__global__ void ls_solve_kernel(const double* __restrict__ sums, float* __restrict__ st) {
+  const double a00 = sums[0], a01 = sums[1], b0 = sums[2], b1 = sums[3], a11 = sums[4];
+  const double det = a00 * a11 - a01 * a01;
+  double x0 = 1.0, x1 = 0.0;
+  if (det != 0.0) {
+    x0 = (a11 * b0 - a01 * b1) / det;
+    x1 = (-a01 * b0 + a00 * b1) / det;
+  }
+  st[0] = (float)x0;
+  st[1] = (float)x1;
+}
+
+__global__ void __launch_bounds__(256) scale_clamp_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                         const float* __restrict__ st, long long count) {
+  const float s = st[0], t = st[1];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x)
+    out[i] = fmaxf(__fadd_rn(__fmul_rn(in[i], s), t), 0.f);
+}
+
+__global__ void __launch_bounds__(256) blend_kernel(float* __restrict__ inout, const float* __restrict__ post,
+                                                   const float* __restrict__ st, int n, long long frame_elems) {
+  const float s = st[0], t = st[1];
+  const int f = blockIdx.y;
+  // python-float weights (utils/util.py:69-70): 0, i*(1/(n-1)), ..., 1, applied to f32 arrays (stay f32)
+  const double step = 1.0 / (double)(n - 1);
+  const double wd = (f == 0) ? 0.0 : (f == n - 1 ? 1.0 : f * step);
+  const float w1 = (float)wd, w0 = (float)(1.0 - wd);
+  float* a = inout + (long long)f * frame_elems;
+  const float* b = post + (long long)f * frame_elems;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < frame_elems;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float pv = fmaxf(__fadd_rn(__fmul_rn(b[i], s), t), 0.f);
+    a[i] = __fadd_rn(__fmul_rn(a[i], w0), __fmul_rn(pv, w1));
+  }
+}
+
+}  // namespace
+
+extern "C" int vda_preprocess_u8(const uint8_t* frames, float* out, int32_t n, int32_t fh, int32_t fw, int32_t oh,
+                                 int32_t ow, vda_stream_t stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const long long total = (long long)n * oh * ow;
+  // cv2: inv_scale = dsize/ssize (double), scale = 1/inv_scale
+  const double sx = 1.0 / ((double)ow / (double)fw), sy = 1.0 / ((double)oh / (double)fh);
+  preprocess_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(frames, out, fh, fw, oh, ow, sy, sx, total);
+  VDA_CUDA_LAUNCH_CHECK("preprocess_kernel");
+  return 0;
+}
+
+extern "C" int vda_resize_depth(const void* in, int32_t dtype, float* out, int32_t n, int32_t ih, int32_t iw, int32_t oh,
+                                int32_t ow, vda_stream_t stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const float rh = oh > 1 ? (float)(ih - 1) / (float)(oh - 1) : 0.f;
+  const float rw = ow > 1 ? (float)(iw - 1) / (float)(ow - 1) : 0.f;
+  const long long total = (long long)n * oh * ow;
+  const unsigned grid = (unsigned)((total + 255) / 256);
+  if (dtype == VDA_BF16) resize_depth_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)in, out, ih, iw, oh, ow, rh, rw, total);
+  else resize_depth_kernel<float><<<grid, 256, 0, st>>>((const float*)in, out, ih, iw, oh, ow, rh, rw, total);
+  VDA_CUDA_LAUNCH_CHECK("resize_depth_kernel");
+  return 0;
+}
+
+extern "C" int vda_scale_shift(const float* pred, const float* target, int64_t count, double* scratch, float* st,
+                               int32_t phase, vda_stream_t stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (phase & 1) {
+    cudaError_t ce = cudaMemsetAsync(scratch, 0, 5 * sizeof(double), s);
+    if (ce != cudaSuccess) {
+      vda_set_error("vda_scale_shift: memset failed: %s", cudaGetErrorString(ce));
+      return (int)ce;
+    }
+  }
+  int blocks = (int)((count + 256 * 8 - 1) / (256 * 8));
+  if (blocks > 4 * vda_sm_count()) blocks = 4 * vda_sm_count();
+  if (blocks < 1) blocks = 1;
+  ls_sums_kernel<<<blocks, 256, 0, s>>>(pred, target, count, scratch);
+  if (phase & 2) ls_solve_kernel<<<1, 1, 0, s>>>(scratch, st);
+  VDA_CUDA_LAUNCH_CHECK("scale_shift kernels");
+  return 0;
+}
+
+extern "C" int vda_scale_clamp(const float* in, float* out, const float* st, int64_t count, vda_stream_t stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  int blocks = (int)((count + 256 * 4 - 1) / (256 * 4));
+  if (blocks > 8 * vda_sm_count()) blocks = 8 * vda_sm_count();
+  if (blocks < 1) blocks = 1;
+  scale_clamp_kernel<<<blocks, 256, 0, s>>>(in, out, st, count);
+  VDA_CUDA_LAUNCH_CHECK("scale_clamp_kernel");
+  return 0;
+}
+
+extern "C" int vda_blend(float* inout, const float* post, const float* st, int32_t n, int64_t frame_elems,
+                         vda_stream_t stream) {
+  VDA_CHECK_ARG(n >= 2, "vda_blend: n must be >= 2");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  int bx = (int)((frame_elems + 256 * 4 - 1) / (256 * 4));
+  if (bx > 2 * vda_sm_count()) bx = 2 * vda_sm_count();
+  if (bx < 1) bx = 1;
+  blend_kernel<<<dim3(bx, n), 256, 0, s>>>(inout, post, st, n, frame_elems);
+  VDA_CUDA_LAUNCH_CHECK("blend_kernel");
+  return 0;
+}

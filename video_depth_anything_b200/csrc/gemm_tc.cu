@@ -1,0 +1,215 @@
+// tcgen05 / TMEM / TMA GEMM with fused epilogues (bf16 operands, fp32 accumulation in tensor memory).
+//
+// Persistent, warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM owner), warps 2..9 = epilogue.
+// Tile 128 x BN x 64, UMMA 128 x BN x 16 (cta_group::1), STAGES-deep smem ring, two TMEM accumulator stages so the
+// epilogue of tile i overlaps the main loop of tile i+1.  A 3x3 convolution is the same kernel: with padded
+// channels-last activations each tap is a constant row offset of the A tensor map (K loop = 9 taps x K/64).
+#include "epilogue.cuh"
+#include "ptx.cuh"
+#include "tmap.h"
+
+namespace {
+
+constexpr int BM = 128, BK = 64;
+constexpr int NUM_EPI_WARPS = 8;
+constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
+
+template <int BN>
+struct TcCfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
+  static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;  // power of two for BN in {32,64,128,256}
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct TcArgs {
+  int M, N, K;         // K per tap
+  int taps, ksplit;    // K loop = ksplit * taps * ceil(K/64)
+  int W2;              // gw + 2 (tap row offsets)
+  int tiles_m, tiles_n;
+};
+
+template <int BN, typename TO, bool RB>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcArgs a,
+               const Epi e) {
+  using C = TcCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* full = bars;                     // [STAGES]   TMA -> MMA
+  uint64_t* empty = bars + C::STAGES;        // [STAGES]   MMA -> TMA
+  uint64_t* tfull = bars + 2 * C::STAGES;    // [2]        MMA -> epilogue
+  uint64_t* tempty = bars + 2 * C::STAGES + 2;  // [2]     epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kb_per_tap = (a.K + BK - 1) / BK;
+  const int num_kb = a.ksplit * a.taps * kb_per_tap;
+  const int num_tiles = a.tiles_m * a.tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+    for (int s = 0; s < C::STAGES; ++s) {
+      ptx::mbar_init(&full[s], 1);
+      ptx::mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tfull[s], 1);
+      ptx::mbar_init(&tempty[s], NUM_EPI_WARPS);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / a.tiles_n) * BM, n0 = (tile % a.tiles_n) * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int kin = kb % kb_per_tap, st = kb / kb_per_tap;  // st = s*taps + tap
+          const int tap = st % a.taps;
+          const int off = (a.taps == 9) ? ((tap / 3 - 1) * a.W2 + (tap % 3 - 1)) : 0;
+          ptx::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * C::STAGE_BYTES;
+          uint8_t* sb = sa + C::A_BYTES;
+          ptx::mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
+          ptx::tma_load_2d(sa, &tmA, kin * BK, m0 + off, &full[stage]);
+          ptx::tma_load_2d(sb, &tmB, st * a.K + kin * BK, n0, &full[stage]);
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(BM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        ptx::mbar_wait(&tempty[acc], acc_phase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(&full[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(smem + stage * C::STAGE_BYTES);
+          const uint32_t sb = sa + C::A_BYTES;
+          const uint64_t da = ptx::make_sw128_desc(sa, 16, 1024);
+          const uint64_t db = ptx::make_sw128_desc(sb, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in the (addr >> 4) field
+            ptx::mma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          }
+          ptx::tc_commit(&empty[stage]);
+          if (kb == num_kb - 1) ptx::tc_commit(&tfull[acc]);
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps
+    const int q = warp & 3;                    // TMEM lane quadrant this warp may access
+    const int half = (warp - 2) >> 2;          // which interleaved set of column chunks
+    const int cw = (e.act == VDA_ACT_GEGLU) ? 64 : 32;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile / a.tiles_n) * BM, n0 = (tile % a.tiles_n) * BN;
+      ptx::mbar_wait(&tfull[acc], acc_phase);
+      ptx::tc_fence_after();
+      const int m = m0 + q * 32 + lane;
+      const RowCtx r = make_row_ctx(e, m);
+      const uint32_t trow = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
+      for (int c = half * cw; c < BN; c += 2 * cw) {
+        if (n0 + c >= a.N) break;
+        float v[32], g[32];
+        ptx::tmem_ld32(trow + c, v);
+        if (cw == 64) ptx::tmem_ld32(trow + c + 32, g);
+        ptx::tmem_ld_wait();
+        epi_chunk<TO, RB>(e, r, n0 + c, v, g);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+template <int BN>
+int launch_tc(const vda_gemm_desc* d, cudaStream_t st) {
+  using C = TcCfg<BN>;
+  CUtensorMap tmA, tmB;
+  int rc = vda_make_tmap_2d(&tmA, d->A, (uint64_t)d->K, (uint64_t)d->rowsA, (uint64_t)d->lda * 2, BK, BM);
+  if (rc) return rc;
+  rc = vda_make_tmap_2d(&tmB, d->B, (uint64_t)d->ksplit * d->taps * d->K, (uint64_t)d->N, (uint64_t)d->ldb * 2, BK, BN);
+  if (rc) return rc;
+  TcArgs a;
+  a.M = d->M; a.N = d->N; a.K = d->K; a.taps = d->taps; a.ksplit = d->ksplit; a.W2 = d->gw + 2;
+  a.tiles_m = (d->M + BM - 1) / BM;
+  a.tiles_n = (d->N + BN - 1) / BN;
+  const int tiles = a.tiles_m * a.tiles_n;
+  const int grid = tiles < vda_sm_count() ? tiles : vda_sm_count();
+  Epi e = make_epi(d);
+  auto kern = gemm_tc_kernel<BN, bf16, true>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t ce = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    if (ce != cudaSuccess) {
+      vda_set_error("gemm_tc: cudaFuncSetAttribute(%d) failed: %s", C::SMEM_BYTES, cudaGetErrorString(ce));
+      return (int)ce;
+    }
+    attr_set = true;
+  }
+  kern<<<grid, NUM_THREADS, C::SMEM_BYTES, st>>>(tmA, tmB, a, e);
+  VDA_CUDA_LAUNCH_CHECK("gemm_tc_kernel");
+  return 0;
+}
+
+}  // namespace
+
+int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
+  VDA_CHECK_ARG(d->a_dtype == VDA_BF16 && d->b_dtype == VDA_BF16, "vda_gemm(tc): operands must be bf16");
+  VDA_CHECK_ARG(d->out_dtype == VDA_BF16 && d->round_bf16, "vda_gemm(tc): the tensor-core path is the bf16 build");
+  VDA_CHECK_ARG((d->lda % 8) == 0 && (d->ldb % 8) == 0, "vda_gemm(tc): lda/ldb must be multiples of 8 elements (TMA)");
+  VDA_CHECK_ARG(((uintptr_t)d->A % 16) == 0 && ((uintptr_t)d->B % 16) == 0, "vda_gemm(tc): operands must be 16B aligned");
+  VDA_CHECK_ARG(d->act != VDA_ACT_GEGLU || d->N % 64 == 0, "vda_gemm(tc): GEGLU needs N %% 64 == 0");
+  VDA_CHECK_ARG(d->head_w == nullptr || d->N == 32, "vda_gemm(tc): fused head needs N == 32");
+  int bn;
+  if (d->N <= 32) bn = 32;
+  else if (d->N <= 64) bn = 64;
+  else if (d->N <= 128 || (d->N % 256 != 0 && d->N % 128 == 0 && d->N < 1024)) bn = 128;
+  else bn = 256;
+  // small problems: prefer more tiles over wide tiles so every SM gets work
+  if (bn == 256 && (int64_t)((d->M + 127) / 128) * ((d->N + 255) / 256) < vda_sm_count()) bn = 128;
+  switch (bn) {
+    case 32: return launch_tc<32>(d, st);
+    case 64: return launch_tc<64>(d, st);
+    case 128: return launch_tc<128>(d, st);
+    default: return launch_tc<256>(d, st);
+  }
+}

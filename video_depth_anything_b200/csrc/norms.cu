@@ -1,0 +1,190 @@
+// LayerNorm (one warp per token row, row held in registers) and GroupNorm over channels-last tokens.
+// HBM-bound: LayerNorm moves 4 B in + 2 B out per element in the bf16 build.
+#include "common.cuh"
+
+namespace {
+
+// ---------------------------------------------------------------- LayerNorm
+template <typename TI, typename TO, bool RB>
+__global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x, TO* __restrict__ y,
+                                                       const float* __restrict__ w, const float* __restrict__ b, float eps,
+                                                       long long rows, int D, int group_rows, int skip_first,
+                                                       const float* __restrict__ pe, int pe_group, int pe_T) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  long long orow = row;
+  if (skip_first) {
+    long long g = row / group_rows;
+    int i = (int)(row % group_rows);
+    if (i == 0) return;
+    orow = g * (group_rows - 1) + i - 1;
+  }
+  constexpr int MAXV = 4;  // up to 4 x 8 x 32 = 1024 channels
+  const int nv = D >> 3;   // 8-element vectors per row
+  float v[MAXV][8];
+  const TI* xr = x + row * D;
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    int c = lane + 32 * j;
+    if (c < nv) {
+      Vec8<TI>::load(xr + c * 8, v[j]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s += v[j][i];
+    }
+  }
+  const float mean = warp_sum(s) / (float)D;
+  float ss = 0.f;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    int c = lane + 32 * j;
+    if (c < nv) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float d = v[j][i] - mean;
+        ss = fmaf(d, d, ss);
+      }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(ss) / (float)D + eps);
+  const float* per = pe ? pe + (long long)((row / pe_group) % pe_T) * D : nullptr;
+  TO* yr = y + orow * D;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    int c = lane + 32 * j;
+    if (c < nv) {
+      float o[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        int ch = c * 8 + i;
+        float t = w[ch] * (rstd * (v[j][i] - mean)) + b[ch];
+        if (per) t = t + per[ch];
+        o[i] = R<RB>(t);
+      }
+      Vec8<TO>::store(yr + c * 8, o);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- GroupNorm
+// pass 1: per (frame, group) sum and sum of squares (fp32 partials, fp64 atomics).
+template <typename TI>
+__global__ void __launch_bounds__(256) gn_stats_kernel(const TI* __restrict__ x, double* __restrict__ stats, int hw, int C,
+                                                      int groups, int rows_per_block) {
+  __shared__ float sh[64][2];
+  const int f = blockIdx.y;
+  const int nv = C >> 3;
+  const int cv = threadIdx.x % nv, rsub = threadIdx.x / nv, rstep = blockDim.x / nv;
+  const int cpg = C / groups;
+  for (int i = threadIdx.x; i < groups * 2; i += blockDim.x) (&sh[0][0])[i] = 0.f;
+  __syncthreads();
+  float s[8] = {}, q[8] = {};
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(hw, r0 + rows_per_block);
+  if (rsub < rstep) {
+    for (int r = r0 + rsub; r < r1; r += rstep) {
+      float v[8];
+      Vec8<TI>::load(x + ((long long)f * hw + r) * C + cv * 8, v);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        s[i] += v[i];
+        q[i] = fmaf(v[i], v[i], q[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      int g = (cv * 8 + i) / cpg;
+      atomicAdd(&sh[g][0], s[i]);
+      atomicAdd(&sh[g][1], q[i]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < groups; i += blockDim.x) {
+    atomicAdd(&stats[((long long)f * groups + i) * 2 + 0], (double)sh[i][0]);
+    atomicAdd(&stats[((long long)f * groups + i) * 2 + 1], (double)sh[i][1]);
+  }
+}
+
+// pass 2: y = a*x + b' with a = rstd*w, b' = -a*mean + bias (the fused-parameter form ATen uses).
+template <typename TI, typename TO, bool RB>
+__global__ void __launch_bounds__(256) gn_apply_kernel(const TI* __restrict__ x, TO* __restrict__ y,
+                                                      const double* __restrict__ stats, const float* __restrict__ w,
+                                                      const float* __restrict__ b, float eps, int hw, int C, int groups,
+                                                      long long total_vec) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total_vec) return;
+  const int nv = C >> 3;
+  const int cv = (int)(idx % nv);
+  const long long row = idx / nv;
+  const int f = (int)(row / hw);
+  const int cpg = C / groups;
+  const double cnt = (double)hw * cpg;
+  float v[8], o[8];
+  Vec8<TI>::load(x + row * C + cv * 8, v);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    int ch = cv * 8 + i, g = ch / cpg;
+    double su = stats[((long long)f * groups + g) * 2], sq = stats[((long long)f * groups + g) * 2 + 1];
+    double mean = su / cnt;
+    double var = sq / cnt - mean * mean;
+    if (var < 0) var = 0;
+    float rstd = rsqrtf((float)var + eps);
+    float a = rstd * w[ch];
+    float bb = -a * (float)mean + b[ch];
+    o[i] = R<RB>(a * v[i] + bb);
+  }
+  Vec8<TO>::store(y + row * C + cv * 8, o);
+}
+
+}  // namespace
+
+extern "C" int vda_layernorm(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, const float* w, const float* b,
+                             float eps, int64_t rows, int32_t D, int32_t group_rows, int32_t skip_first, const float* pe,
+                             int32_t pe_group, int32_t pe_T, vda_stream_t stream) {
+  VDA_CHECK_ARG(D % 8 == 0 && D <= 1024, "vda_layernorm: D=%d must be a multiple of 8 and <= 1024", D);
+  VDA_CHECK_ARG(!skip_first || group_rows > 1, "vda_layernorm: skip_first needs group_rows");
+  VDA_CHECK_ARG(!pe || (pe_group > 0 && pe_T > 0), "vda_layernorm: pe needs pe_group, pe_T");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int wpb = 8;
+  const unsigned grid = (unsigned)((rows + wpb - 1) / wpb);
+#define LN(TI, TO, RB)                                                                                          \
+  layernorm_kernel<TI, TO, RB><<<grid, wpb * 32, 0, st>>>((const TI*)x, (TO*)y, w, b, eps, rows, D, group_rows, \
+                                                          skip_first, pe, pe_group, pe_T)
+  if (x_dtype == VDA_F32 && y_dtype == VDA_BF16) LN(float, bf16, true);
+  else if (x_dtype == VDA_BF16 && y_dtype == VDA_BF16) LN(bf16, bf16, true);
+  else if (x_dtype == VDA_F32 && y_dtype == VDA_F32) LN(float, float, false);
+  else VDA_CHECK_ARG(false, "vda_layernorm: unsupported dtypes %d -> %d", x_dtype, y_dtype);
+#undef LN
+  VDA_CUDA_LAUNCH_CHECK("layernorm_kernel");
+  return 0;
+}
+
+extern "C" int vda_groupnorm_tokens(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, const float* w,
+                                    const float* b, float eps, int32_t frames, int32_t hw, int32_t C, int32_t groups,
+                                    double* stats, vda_stream_t stream) {
+  VDA_CHECK_ARG(C % 8 == 0 && C % groups == 0 && groups <= 64 && C / 8 <= 256, "vda_groupnorm_tokens: bad C=%d groups=%d",
+                C, groups);
+  VDA_CHECK_ARG(x_dtype == y_dtype, "vda_groupnorm_tokens: x/y dtypes must match");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  cudaError_t ce = cudaMemsetAsync(stats, 0, sizeof(double) * 2 * frames * groups, st);
+  if (ce != cudaSuccess) {
+    vda_set_error("vda_groupnorm_tokens: memset failed: %s", cudaGetErrorString(ce));
+    return (int)ce;
+  }
+  int blocks_per_frame = (hw + 255) / 256;
+  if (blocks_per_frame > 32) blocks_per_frame = 32;
+  const int rpb = (hw + blocks_per_frame - 1) / blocks_per_frame;
+  dim3 g1(blocks_per_frame, frames);
+  const long long total_vec = (long long)frames * hw * (C / 8);
+  const unsigned g2 = (unsigned)((total_vec + 255) / 256);
+  if (x_dtype == VDA_BF16) {
+    gn_stats_kernel<bf16><<<g1, 256, 0, st>>>((const bf16*)x, stats, hw, C, groups, rpb);
+    gn_apply_kernel<bf16, bf16, true><<<g2, 256, 0, st>>>((const bf16*)x, (bf16*)y, stats, w, b, eps, hw, C, groups, total_vec);
+  } else {
+    gn_stats_kernel<float><<<g1, 256, 0, st>>>((const float*)x, stats, hw, C, groups, rpb);
+    gn_apply_kernel<float, float, false><<<g2, 256, 0, st>>>((const float*)x, (float*)y, stats, w, b, eps, hw, C, groups, total_vec);
+  }
+  VDA_CUDA_LAUNCH_CHECK("groupnorm kernels");
+  return 0;
+}

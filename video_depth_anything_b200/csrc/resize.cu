@@ -1,0 +1,158 @@
+// Memory-bound layout / resampling kernels of the forward pass: bilinear (align_corners=True) on channels-last
+// maps, patch-embed im2col, class-token rows, bicubic resampling of the position grid.
+#include "common.cuh"
+
+namespace {
+
+// ATen upsample_bilinear2d semantics (align_corners=True): src = dst * (in-1)/(out-1), lambda in fp32,
+// value = h0*(w0*a + w1*b) + h1*(w0*c + w1*d), computed in fp32 and rounded once to the storage type.
+template <typename T>
+__global__ void __launch_bounds__(256) bilinear_kernel(const T* __restrict__ in, T* __restrict__ out, int ih, int iw,
+                                                      int ipad, int oh, int ow, int opad, int C, float rh, float rw,
+                                                      long long total_vec) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total_vec) return;
+  const int nv = C >> 3;
+  const int cv = (int)(idx % nv);
+  long long pix = idx / nv;
+  const int ox = (int)(pix % ow);
+  pix /= ow;
+  const int oy = (int)(pix % oh);
+  const int f = (int)(pix / oh);
+  const float h1r = rh * oy;
+  const int h1 = (int)h1r;
+  const int h1p = (h1 < ih - 1) ? 1 : 0;
+  const float h1l = h1r - h1, h0l = 1.f - h1l;
+  const float w1r = rw * ox;
+  const int w1 = (int)w1r;
+  const int w1p = (w1 < iw - 1) ? 1 : 0;
+  const float w1l = w1r - w1, w0l = 1.f - w1l;
+  const int IW = iw + 2 * ipad, IH = ih + 2 * ipad;
+  const T* base = in + (((long long)f * IH + h1 + ipad) * IW + w1 + ipad) * C + cv * 8;
+  float a[8], b[8], c[8], d[8], o[8];
+  Vec8<T>::load(base, a);
+  Vec8<T>::load(base + (long long)w1p * C, b);
+  Vec8<T>::load(base + (long long)h1p * IW * C, c);
+  Vec8<T>::load(base + ((long long)h1p * IW + w1p) * C, d);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) o[i] = h0l * (w0l * a[i] + w1l * b[i]) + h1l * (w0l * c[i] + w1l * d[i]);
+  const int OW = ow + 2 * opad, OH = oh + 2 * opad;
+  Vec8<T>::store(out + (((long long)f * OH + oy + opad) * OW + ox + opad) * C + cv * 8, o);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) im2col_patch_kernel(const float* __restrict__ x, T* __restrict__ A, int H, int W,
+                                                          int kpad, long long total) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int k = (int)(idx % kpad);
+  const long long m = idx / kpad;
+  const int pw = W / 14, ph = H / 14;
+  const int px = (int)(m % pw);
+  const int py = (int)((m / pw) % ph);
+  const int f = (int)(m / ((long long)pw * ph));
+  float v = 0.f;
+  if (k < 588) {
+    const int c = k / 196, r = k % 196, i = r / 14, j = r % 14;
+    v = x[(((long long)f * 3 + c) * H + py * 14 + i) * W + px * 14 + j];
+  }
+  A[idx] = from_f32<T>(v);
+}
+
+__global__ void cls_rows_kernel(float* __restrict__ resid, const float* __restrict__ cls, const float* __restrict__ pos,
+                                int frames, int ntok, int D) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= frames * D) return;
+  const int f = idx / D, c = idx % D;
+  resid[(long long)f * ntok * D + c] = __fadd_rn(cls[c], pos[c]);
+}
+
+// ATen upsample_bicubic2d (align_corners=False, scale_factor given, A = -0.75): src = (dst + 0.5)/scale - 0.5,
+// taps floor(src)-1..+2 with clamped indices.
+__device__ __forceinline__ float cubic1(float x, float A) { return ((A + 2) * x - (A + 3)) * x * x + 1; }
+__device__ __forceinline__ float cubic2(float x, float A) { return ((A * x - 5 * A) * x + 8 * A) * x - 4 * A; }
+__device__ __forceinline__ void cubic_coeffs(float t, float* c) {
+  const float A = -0.75f;
+  c[0] = cubic2(t + 1.f, A);
+  c[1] = cubic1(t, A);
+  c[2] = cubic1(1.f - t, A);
+  c[3] = cubic2(2.f - t, A);
+}
+__global__ void pos_bicubic_kernel(const float* __restrict__ pos, float* __restrict__ out, int D, int src, int oh, int ow,
+                                   float inv_sh, float inv_sw) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)oh * ow * D) return;
+  const int c = (int)(idx % D);
+  const int ox = (int)((idx / D) % ow), oy = (int)(idx / ((long long)D * ow));
+  const float sy = inv_sh * (oy + 0.5f) - 0.5f, sx = inv_sw * (ox + 0.5f) - 0.5f;
+  const int iy = (int)floorf(sy), ix = (int)floorf(sx);
+  float cy[4], cx[4];
+  cubic_coeffs(sy - iy, cy);
+  cubic_coeffs(sx - ix, cx);
+  float acc = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int yy = min(max(iy - 1 + i, 0), src - 1);
+    float row = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int xx = min(max(ix - 1 + j, 0), src - 1);
+      row += pos[((long long)(1 + yy * src + xx)) * D + c] * cx[j];
+    }
+    acc += row * cy[i];
+  }
+  out[(long long)(1 + oy * ow + ox) * D + c] = acc;
+  if (idx < D) out[c] = pos[c];  // class-token position row is copied through
+}
+
+}  // namespace
+
+extern "C" int vda_bilinear(const void* in, void* out, int32_t dtype, int32_t frames, int32_t ih, int32_t iw,
+                            int32_t in_padded, int32_t oh, int32_t ow, int32_t out_padded, int32_t C,
+                            vda_stream_t stream) {
+  VDA_CHECK_ARG(C % 8 == 0, "vda_bilinear: C=%d must be a multiple of 8", C);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const float rh = oh > 1 ? (float)(ih - 1) / (float)(oh - 1) : 0.f;
+  const float rw = ow > 1 ? (float)(iw - 1) / (float)(ow - 1) : 0.f;
+  const long long total = (long long)frames * oh * ow * (C / 8);
+  const unsigned grid = (unsigned)((total + 255) / 256);
+  if (dtype == VDA_BF16)
+    bilinear_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)in, (bf16*)out, ih, iw, in_padded ? 1 : 0, oh, ow,
+                                                out_padded ? 1 : 0, C, rh, rw, total);
+  else
+    bilinear_kernel<float><<<grid, 256, 0, st>>>((const float*)in, (float*)out, ih, iw, in_padded ? 1 : 0, oh, ow,
+                                                 out_padded ? 1 : 0, C, rh, rw, total);
+  VDA_CUDA_LAUNCH_CHECK("bilinear_kernel");
+  return 0;
+}
+
+extern "C" int vda_im2col_patch(const float* x, void* A, int32_t a_dtype, int32_t frames, int32_t H, int32_t W,
+                                int32_t kpad, vda_stream_t stream) {
+  VDA_CHECK_ARG(H % 14 == 0 && W % 14 == 0, "vda_im2col_patch: H, W must be multiples of 14 (patch_embed.py:73-74)");
+  VDA_CHECK_ARG(kpad >= 588, "vda_im2col_patch: kpad < 588");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const long long total = (long long)frames * (H / 14) * (W / 14) * kpad;
+  const unsigned grid = (unsigned)((total + 255) / 256);
+  if (a_dtype == VDA_BF16) im2col_patch_kernel<bf16><<<grid, 256, 0, st>>>(x, (bf16*)A, H, W, kpad, total);
+  else im2col_patch_kernel<float><<<grid, 256, 0, st>>>(x, (float*)A, H, W, kpad, total);
+  VDA_CUDA_LAUNCH_CHECK("im2col_patch_kernel");
+  return 0;
+}
+
+extern "C" int vda_cls_rows(float* resid, const float* cls, const float* pos, int32_t frames, int32_t ntok, int32_t D,
+                            vda_stream_t stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  cls_rows_kernel<<<(frames * D + 255) / 256, 256, 0, st>>>(resid, cls, pos, frames, ntok, D);
+  VDA_CUDA_LAUNCH_CHECK("cls_rows_kernel");
+  return 0;
+}
+
+extern "C" int vda_pos_embed_bicubic(const float* pos, float* out, int32_t D, int32_t src, int32_t oh, int32_t ow,
+                                     double scale_h, double scale_w, vda_stream_t stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const long long total = (long long)oh * ow * D;
+  pos_bicubic_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(pos, out, D, src, oh, ow, (float)(1.0 / scale_h),
+                                                                      (float)(1.0 / scale_w));
+  VDA_CUDA_LAUNCH_CHECK("pos_bicubic_kernel");
+  return 0;
+}

@@ -1,0 +1,194 @@
+"""The sliding-window driver: `VideoDepthAnything.infer_video_depth` (reference video_depth.py:329-417).
+
+What the reference does on the host with cv2 / numpy (pre-processing 32x per window, per-frame D2H, numpy
+least squares and blending) runs here on the device, asynchronously on one stream: every source frame is
+pre-processed once, windows gather their 32 inputs by index (the window contents are pure index arithmetic,
+video_depth.py:350-364), and the sequential scale/shift recurrence keeps (scale, shift) in device memory, so there
+is exactly one device->host copy: the final [N, H, W] stack.
+
+Window-level data parallelism: with `torch.distributed` initialised, windows are dealt to
+ranks in contiguous blocks; every rank runs its forwards, rank 0 gathers the raw per-window depth maps (NCCL) and
+runs the cheap sequential stitching pass.  No collective runs inside a forward.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import lib as L
+
+INFER_LEN = 32
+OVERLAP = 10
+KEYFRAMES = [0, 12, 24, 25, 26, 27, 28, 29, 30, 31]
+INTERP_LEN = 8
+FRAME_STEP = INFER_LEN - OVERLAP
+ALIGN_LEN = OVERLAP - INTERP_LEN
+
+
+def effective_input_size(frame_h: int, frame_w: int, input_size: int) -> int:
+    """video_depth.py:330-334."""
+    ratio = max(frame_h, frame_w) / min(frame_h, frame_w)
+    if ratio > 1.78:
+        input_size = int(input_size * 1.777 / ratio)
+        input_size = round(input_size / 14) * 14
+    return input_size
+
+
+def network_size(frame_h: int, frame_w: int, input_size: int, multiple: int = 14):
+    """`Resize.get_size`, keep_aspect_ratio + 'lower_bound' + ensure_multiple_of=14 (util/transform.py:51-107)."""
+
+    def constrain(x, min_val):
+        y = int(np.round(x / multiple) * multiple)
+        if y < min_val:
+            y = int(np.ceil(x / multiple) * multiple)
+        return y
+
+    scale_h, scale_w = input_size / frame_h, input_size / frame_w
+    if scale_w > scale_h:
+        scale_h = scale_w
+    else:
+        scale_w = scale_h
+    return constrain(scale_h * frame_h, input_size), constrain(scale_w * frame_w, input_size)
+
+
+def window_index_map(n_frames: int) -> np.ndarray:
+    """[n_windows, 32] source-frame index of every window slot (video_depth.py:350-364,374)."""
+    append = (FRAME_STEP - (n_frames % FRAME_STEP)) % FRAME_STEP + (INFER_LEN - FRAME_STEP)
+    padded = np.concatenate([np.arange(n_frames), np.full(append, n_frames - 1)]).astype(np.int64)
+    starts = range(0, n_frames, FRAME_STEP)
+    idx = np.stack([padded[s:s + INFER_LEN] for s in starts])
+    for k in range(1, idx.shape[0]):
+        idx[k, :OVERLAP] = idx[k - 1, KEYFRAMES]
+    return idx
+
+
+def shard_windows(n_windows: int, world: int):
+    """Contiguous blocks of windows per rank; [(first, count)] * world."""
+    per = (n_windows + world - 1) // world
+    out = []
+    for r in range(world):
+        lo = min(r * per, n_windows)
+        out.append((lo, max(0, min(per, n_windows - lo))))
+    return out
+
+
+class WindowedDepthDriver:
+    def __init__(self, model, device="cuda", fp32=False, skip_tmp_block=False, upload_chunk=64):
+        self.model = model
+        self.device = torch.device(device)
+        if self.device.type == "cuda" and self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        L.require_device(self.device)
+        self.fp32 = fp32
+        self.skip_tmp_block = skip_tmp_block
+        self.upload_chunk = upload_chunk
+        self.lib = L.load()
+        self.last_scale_shift = None
+
+    # ------------------------------------------------------------------ stages
+    def preprocess(self, frames, ids, nh, nw):
+        """Source frames `ids` (sorted unique) -> {id: row} and device tensor [len(ids), 3, nh, nw] fp32
+        (util/transform.py:109-158 + video_depth.py:361, once per source frame)."""
+        fh, fw = frames[0].shape[:2]
+        out = torch.empty((len(ids), 3, nh, nw), dtype=torch.float32, device=self.device)
+        st = L.stream_ptr()
+        for c0 in range(0, len(ids), self.upload_chunk):
+            chunk = ids[c0:c0 + self.upload_chunk]
+            host = np.ascontiguousarray(np.stack([np.asarray(frames[int(i)]) for i in chunk]))
+            if host.dtype != np.uint8:
+                raise TypeError("frames must be uint8 [N,H,W,3]")
+            dev = torch.from_numpy(host).to(self.device, non_blocking=True)
+            L.check(self.lib.vda_preprocess_u8(dev.data_ptr(), out[c0].data_ptr(), len(chunk), fh, fw, nh, nw, st),
+                    "vda_preprocess_u8")
+            del dev
+        return {int(i): r for r, i in enumerate(ids)}, out
+
+    def forward_windows(self, pre, rowmap, idx_rows, nh, nw, fh, fw):
+        """Run the network on the given windows; returns raw depth [n_win*32, fh, fw] fp32 on device."""
+        bf16 = not self.fp32
+        plan = self.model.plan(1, INFER_LEN, nh, nw, self.device, bf16, self.skip_tmp_block)
+        raw = torch.empty((len(idx_rows) * INFER_LEN, fh, fw), dtype=torch.float32, device=self.device)
+        st = L.stream_ptr()
+        sel_all = torch.as_tensor([[rowmap[int(i)] for i in row] for row in idx_rows], dtype=torch.int64).to(self.device)
+        for k in range(len(idx_rows)):
+            torch.index_select(pre, 0, sel_all[k], out=plan.x_in)
+            plan.launch()
+            L.check(self.lib.vda_resize_depth(plan.depth.data_ptr(), plan.dcode, raw[k * INFER_LEN].data_ptr(), INFER_LEN,
+                                              nh, nw, fh, fw, st), "vda_resize_depth")
+        return raw
+
+    def stitch(self, raw, n_frames):
+        """Scale/shift alignment + overlap blend over all windows (video_depth.py:379-417), on device."""
+        n_win = raw.shape[0] // INFER_LEN
+        fh, fw = raw.shape[1:]
+        fe = fh * fw
+        total = INFER_LEN + FRAME_STEP * (n_win - 1)
+        out = torch.empty((total, fh, fw), dtype=torch.float32, device=self.device)
+        out[:INFER_LEN].copy_(raw[:INFER_LEN])
+        ref = torch.stack([raw[KEYFRAMES[0]], raw[KEYFRAMES[1]]]).contiguous()   # frame 0 of the video + slot 12
+        st_all = torch.zeros((n_win, 2), dtype=torch.float32, device=self.device)
+        st_all[0, 0] = 1.0
+        scratch = torch.zeros(5, dtype=torch.float64, device=self.device)
+        s = L.stream_ptr()
+        pos = INFER_LEN
+        for k in range(1, n_win):
+            cur = raw[k * INFER_LEN:(k + 1) * INFER_LEN]
+            stp = st_all[k].data_ptr()
+            L.check(self.lib.vda_scale_shift(cur.data_ptr(), ref.data_ptr(), ALIGN_LEN * fe, scratch.data_ptr(), stp, 3, s),
+                    "vda_scale_shift")
+            L.check(self.lib.vda_blend(out[pos - INTERP_LEN].data_ptr(), cur[ALIGN_LEN].data_ptr(), stp, INTERP_LEN, fe, s),
+                    "vda_blend")
+            L.check(self.lib.vda_scale_clamp(cur[OVERLAP].data_ptr(), out[pos].data_ptr(), stp, FRAME_STEP * fe, s),
+                    "vda_scale_clamp")
+            L.check(self.lib.vda_scale_clamp(cur[KEYFRAMES[1]].data_ptr(), ref[1].data_ptr(), stp, fe, s), "vda_scale_clamp")
+            pos += FRAME_STEP
+        self.last_scale_shift = st_all
+        return out[:n_frames]
+
+    # ------------------------------------------------------------------ whole job
+    def run(self, frames, input_size=518, return_device=False):
+        n = frames.shape[0]
+        fh, fw = frames[0].shape[:2]
+        isz = effective_input_size(fh, fw, input_size)
+        nh, nw = network_size(fh, fw, isz)
+        idx = window_index_map(n)
+        dist = torch.distributed
+        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        rank = dist.get_rank() if world > 1 else 0
+        first, count = shard_windows(idx.shape[0], world)[rank]
+        mine = idx[first:first + count]
+        with torch.cuda.device(self.device), torch.no_grad():
+            if count > 0:
+                ids = np.unique(mine)
+                rowmap, pre = self.preprocess(frames, ids, nh, nw)
+                raw = self.forward_windows(pre, rowmap, mine, nh, nw, fh, fw)
+                del pre
+            else:
+                raw = torch.empty((0, fh, fw), dtype=torch.float32, device=self.device)
+            if world > 1:
+                raw = self._gather_raw(raw, idx.shape[0], world, rank, fh, fw)
+                if rank != 0:
+                    return None
+            depth = self.stitch(raw, n)
+            if return_device:
+                return depth
+            return depth.cpu().numpy()
+
+    def _gather_raw(self, raw, n_win, world, rank, fh, fw):
+        """Raw depth blocks of every rank -> rank 0 (point-to-point over NCCL / NVLink; sizes are index arithmetic)."""
+        dist = torch.distributed
+        shards = shard_windows(n_win, world)
+        if rank == 0:
+            full = torch.empty((n_win * INFER_LEN, fh, fw), dtype=torch.float32, device=self.device)
+            full[:raw.shape[0]].copy_(raw)
+            reqs = []
+            for r in range(1, world):
+                lo, cnt = shards[r]
+                if cnt:
+                    reqs.append(dist.irecv(full[lo * INFER_LEN:(lo + cnt) * INFER_LEN], src=r))
+            for q in reqs:
+                q.wait()
+            return full
+        if raw.shape[0]:
+            dist.send(raw, dst=0)
+        return raw

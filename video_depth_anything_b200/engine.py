@@ -1,0 +1,441 @@
+"""Host side of the forward pass: weight packing and the per-shape launch plan.
+
+`PackedWeights` turns the reference-layout state dict into the K-major matrices the kernels consume (once per
+device / precision).  `ForwardPlan` owns every activation buffer for one (frames, H, W) shape and a flat list of
+pre-built kernel launches; running the plan is a loop of ctypes calls on the current CUDA stream -- no allocation,
+no host synchronisation, so it can also be captured into a CUDA graph.
+
+Data layout: every activation is token-major / channels-last ([rows, C] row-major); feature maps that feed a 3x3
+convolution carry a zero one-pixel border per frame ("padded", see include/vda.h).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+
+from . import lib as L
+from .modules import ENCODERS
+
+KPAD_PATCH = 640  # 3*14*14 = 588 padded to a multiple of the 64-wide K block
+
+
+def _conv3x3_pack(w: torch.Tensor) -> torch.Tensor:
+    """[Cout, Cin, 3, 3] -> [Cout, 9*Cin], k = (dy*3+dx)*Cin + ci."""
+    co, ci = w.shape[:2]
+    return w.permute(0, 2, 3, 1).reshape(co, 9 * ci).contiguous()
+
+
+def _convt_pack(w: torch.Tensor) -> torch.Tensor:
+    """ConvTranspose2d weight [Cin, Cout, k, k] -> [(ky*k+kx)*Cout + co, Cin]."""
+    ci, co, k, _ = w.shape
+    return w.permute(2, 3, 1, 0).reshape(k * k * co, ci).contiguous()
+
+
+def _geglu_interleave(t: torch.Tensor) -> torch.Tensor:
+    """Rows [value(4C) ; gate(4C)] -> groups of 64 rows = 32 value rows followed by their 32 gate rows."""
+    half = t.shape[0] // 2
+    v, g = t[:half], t[half:]
+    v = v.reshape(half // 32, 32, *t.shape[1:])
+    g = g.reshape(half // 32, 32, *t.shape[1:])
+    return torch.cat([v, g], dim=1).reshape(t.shape).contiguous()
+
+
+class PackedWeights:
+    """All weights of one model on one device in one precision (bf16 build or fp32 build)."""
+
+    def __init__(self, model, device, bf16: bool):
+        self.bf16 = bf16
+        wdt = torch.bfloat16 if bf16 else torch.float32
+        sd = {k: v.detach().to(device=device, dtype=torch.float32) for k, v in model.state_dict().items()}
+        self.encoder = model.encoder
+        enc = ENCODERS[model.encoder]
+        D = enc["dim"]
+        self.D, self.heads, self.depth, self.taps = D, enc["heads"], enc["depth"], enc["taps"]
+        self.features = sd["head.scratch.layer1_rn.weight"].shape[0]
+        self.oc = [sd[f"head.projects.{i}.weight"].shape[0] for i in range(4)]
+        w = {}
+
+        def mat(name, t):
+            w[name] = t.to(wdt).contiguous()
+
+        def vec(name, t):
+            w[name] = t.float().contiguous()
+
+        p = "pretrained."
+        pw = torch.zeros(D, KPAD_PATCH, device=device)
+        pw[:, :588] = sd[p + "patch_embed.proj.weight"].reshape(D, 588)
+        mat("patch.w", pw)
+        vec("patch.b", sd[p + "patch_embed.proj.bias"])
+        vec("cls", sd[p + "cls_token"].reshape(D))
+        vec("pos", sd[p + "pos_embed"].reshape(-1, D))
+        for i in range(self.depth):
+            b = f"{p}blocks.{i}."
+            for n in ("norm1", "norm2"):
+                vec(f"b{i}.{n}.w", sd[b + n + ".weight"])
+                vec(f"b{i}.{n}.b", sd[b + n + ".bias"])
+            for n, key in (("qkv", "attn.qkv"), ("proj", "attn.proj"), ("fc1", "mlp.fc1"), ("fc2", "mlp.fc2")):
+                mat(f"b{i}.{n}.w", sd[b + key + ".weight"])
+                vec(f"b{i}.{n}.b", sd[b + key + ".bias"])
+            vec(f"b{i}.ls1", sd[b + "ls1.gamma"])
+            vec(f"b{i}.ls2", sd[b + "ls2.gamma"])
+        vec("norm.w", sd[p + "norm.weight"])
+        vec("norm.b", sd[p + "norm.bias"])
+
+        h = "head."
+        for i in range(4):
+            mat(f"proj{i}.w", sd[f"{h}projects.{i}.weight"].reshape(self.oc[i], D))
+            vec(f"proj{i}.b", sd[f"{h}projects.{i}.bias"])
+        mat("rs0.w", _convt_pack(sd[h + "resize_layers.0.weight"]))
+        vec("rs0.b", sd[h + "resize_layers.0.bias"])
+        mat("rs1.w", _convt_pack(sd[h + "resize_layers.1.weight"]))
+        vec("rs1.b", sd[h + "resize_layers.1.bias"])
+        mat("rs3.w", _conv3x3_pack(sd[h + "resize_layers.3.weight"]))
+        vec("rs3.b", sd[h + "resize_layers.3.bias"])
+        sc = h + "scratch."
+        for i in range(1, 5):
+            mat(f"rn{i}.w", _conv3x3_pack(sd[f"{sc}layer{i}_rn.weight"]))
+            r = f"{sc}refinenet{i}."
+            mat(f"ref{i}.out.w", sd[r + "out_conv.weight"].reshape(self.features, self.features))
+            vec(f"ref{i}.out.b", sd[r + "out_conv.bias"])
+            for u in (1, 2):
+                for c in (1, 2):
+                    mat(f"ref{i}.rcu{u}.c{c}.w", _conv3x3_pack(sd[f"{r}resConfUnit{u}.conv{c}.weight"]))
+                    vec(f"ref{i}.rcu{u}.c{c}.b", sd[f"{r}resConfUnit{u}.conv{c}.bias"])
+        mat("oc1.w", _conv3x3_pack(sd[sc + "output_conv1.weight"]))
+        vec("oc1.b", sd[sc + "output_conv1.bias"])
+        # the fp32 island (dpt_temporal.py:95-97): weights stay fp32; the tensor-core path splits them into bf16 hi + lo
+        w2 = _conv3x3_pack(sd[sc + "output_conv2.0.weight"]).float()
+        w["oc2.w32"] = w2.contiguous()
+        if bf16:
+            hi = w2.to(torch.bfloat16)
+            lo = (w2 - hi.float()).to(torch.bfloat16)
+            w["oc2.whl"] = torch.cat([hi, lo], dim=1).contiguous()
+        vec("oc2.b", sd[sc + "output_conv2.0.bias"])
+        vec("oc2.hw", sd[sc + "output_conv2.2.weight"].reshape(32))
+        self.head_b = float(sd[sc + "output_conv2.2.bias"].reshape(()).item())
+        for m in range(4):
+            t = f"{h}motion_modules.{m}.temporal_transformer."
+            vec(f"mm{m}.gn.w", sd[t + "norm.weight"])
+            vec(f"mm{m}.gn.b", sd[t + "norm.bias"])
+            mat(f"mm{m}.in.w", sd[t + "proj_in.weight"])
+            vec(f"mm{m}.in.b", sd[t + "proj_in.bias"])
+            tb = t + "transformer_blocks.0."
+            for a in (0, 1):
+                ab = f"{tb}attention_blocks.{a}."
+                mat(f"mm{m}.a{a}.qkv.w", torch.cat([sd[ab + "to_q.weight"], sd[ab + "to_k.weight"], sd[ab + "to_v.weight"]], 0))
+                mat(f"mm{m}.a{a}.out.w", sd[ab + "to_out.0.weight"])
+                vec(f"mm{m}.a{a}.out.b", sd[ab + "to_out.0.bias"])
+                vec(f"mm{m}.a{a}.pe", sd[ab + "pos_encoder.pe"][0])
+                vec(f"mm{m}.a{a}.ln.w", sd[f"{tb}norms.{a}.weight"])
+                vec(f"mm{m}.a{a}.ln.b", sd[f"{tb}norms.{a}.bias"])
+            mat(f"mm{m}.ff1.w", _geglu_interleave(sd[tb + "ff.net.0.proj.weight"]))
+            vec(f"mm{m}.ff1.b", _geglu_interleave(sd[tb + "ff.net.0.proj.bias"]))
+            mat(f"mm{m}.ff2.w", sd[tb + "ff.net.2.weight"])
+            vec(f"mm{m}.ff2.b", sd[tb + "ff.net.2.bias"])
+            vec(f"mm{m}.ffln.w", sd[tb + "ff_norm.weight"])
+            vec(f"mm{m}.ffln.b", sd[tb + "ff_norm.bias"])
+            mat(f"mm{m}.po.w", sd[t + "proj_out.weight"])
+            vec(f"mm{m}.po.b", sd[t + "proj_out.bias"])
+        self.w = w
+        self.pe_len = int(sd[f"{h}motion_modules.0.temporal_transformer.transformer_blocks.0.attention_blocks.0.pos_encoder.pe"].shape[1])
+
+
+class ForwardPlan:
+    """Buffers + launch list for `VideoDepthAnything.forward` on x[frames=B*T, 3, H, W] (video_depth.py:58-65)."""
+
+    def __init__(self, pw: PackedWeights, batch: int, T: int, H: int, W: int, device, skip_tmp_block=False, use_tc=None,
+                 keep=()):
+        assert H % 14 == 0 and W % 14 == 0, f"Input image size {H}x{W} is not a multiple of patch size 14"  # patch_embed.py:73-74
+        if T > pw.pe_len:
+            raise ValueError(f"video length {T} exceeds the positional-encoding length {pw.pe_len} (num_frames)")
+        self.pw, self.device = pw, device
+        self.bf16 = pw.bf16
+        self.adt = torch.bfloat16 if pw.bf16 else torch.float32
+        self.dcode = L.BF16 if pw.bf16 else L.F32
+        self.use_tc = bool(pw.bf16) if use_tc is None else bool(use_tc)
+        self.batch, self.T, self.H, self.W = batch, T, H, W
+        self.BT = batch * T
+        self.ph, self.pw_ = H // 14, W // 14
+        self.ops = []      # (callable, args) in launch order
+        self.bufs = {}     # name -> tensor (kept alive; `keep` names are exposed for tap-level tests)
+        self.keep = set(keep)
+        self.n_launches = 0
+        self._ws = None
+        self._ws_need = 0
+        self._lib = L.load()
+        self._build(skip_tmp_block)
+        if not self.use_tc:
+            self._ws = torch.empty(max(self._ws_need, 4), dtype=torch.uint8, device=device)
+            for fn, args in self.ops:
+                if fn is self._lib.vda_gemm:
+                    args[0].workspace = self._ws.data_ptr()
+                    args[0].workspace_bytes = self._ws.numel()
+
+    # ------------------------------------------------------------------ buffer helpers
+    def buf(self, name, rows, cols, dtype=None, zero=False):
+        dtype = dtype or self.adt
+        t = (torch.zeros if zero else torch.empty)((rows, cols), dtype=dtype, device=self.device)
+        self.bufs[name] = t
+        return t
+
+    def padded(self, name, h, w, C):
+        """Zero-bordered channels-last map [BT*(h+2)*(w+2), C]; borders are never written afterwards."""
+        return self.buf(name, self.BT * (h + 2) * (w + 2), C, zero=True)
+
+    # ------------------------------------------------------------------ op builders
+    def gemm(self, A, B, M, N, K, *, rowsA=None, lda=None, taps=1, ksplit=1, geo=None, m_padded=0, bias=None,
+             act=L.ACT_NONE, out=None, ldo=None, out_map=L.MAP_SAME, out_relu=None, res=None, res2=None, ldres=None,
+             res_map=L.MAP_SAME, resid=None, gamma=None, pos=None, resid_map=L.MAP_SAME, resid_assign=0, pos_rows=0,
+             ct_k=0, ct_cout=0, head_w=None, head_out=None, head_b=0.0, use_tc=None, b_dtype=None):
+        d = L.GemmDesc()
+        d.A, d.B = A.data_ptr(), B.data_ptr()
+        d.lda = lda if lda is not None else A.shape[1]
+        d.ldb = B.shape[1]
+        d.rowsA = rowsA if rowsA is not None else A.shape[0]
+        d.a_dtype = L.dt(A)
+        d.b_dtype = L.dt(B) if b_dtype is None else b_dtype
+        d.M, d.N, d.K, d.taps, d.ksplit = M, N, K, taps, ksplit
+        if geo is not None:
+            d.gb, d.gh, d.gw = geo
+        d.m_padded = m_padded
+        d.bias = L._ptr(bias)
+        d.act = act
+        d.round_bf16 = 1 if self.bf16 else 0
+        d.out_dtype = self.dcode
+        d.out = L._ptr(out)
+        d.out_relu = L._ptr(out_relu)
+        ncols = N // 2 if act == L.ACT_GEGLU else (ct_cout if ct_k else N)
+        d.ldo = ldo if ldo is not None else (out.shape[1] if out is not None else ncols)
+        d.out_map = out_map
+        d.ct_k, d.ct_cout = ct_k, ct_cout
+        d.res, d.res2 = L._ptr(res), L._ptr(res2)
+        d.ldres = ldres if ldres is not None else (res.shape[1] if res is not None else d.ldo)
+        d.res_map = res_map
+        d.resid, d.gamma, d.pos = L._ptr(resid), L._ptr(gamma), L._ptr(pos)
+        d.ldresid = resid.shape[1] if resid is not None else 0
+        d.resid_map, d.resid_assign, d.pos_rows = resid_map, resid_assign, pos_rows
+        d.head_w, d.head_out, d.head_b = L._ptr(head_w), L._ptr(head_out), head_b
+        d.use_tc = int(self.use_tc if use_tc is None else use_tc)
+        if not d.use_tc:
+            self._ws_need = max(self._ws_need, M * N * 4)
+        self.ops.append((self._lib.vda_gemm, [d]))
+        self.n_launches += 1 if d.use_tc else 2
+        return d
+
+    def op(self, fn, *args, launches=1):
+        self.ops.append((fn, list(args)))
+        self.n_launches += launches
+
+    def layernorm(self, x, y, w, b, eps, rows, D, group_rows=0, skip_first=0, pe=None, pe_group=0, pe_T=0):
+        self.op(self._lib.vda_layernorm, x.data_ptr(), L.dt(x), y.data_ptr(), L.dt(y), w.data_ptr(), b.data_ptr(), eps,
+                rows, D, group_rows, skip_first, L._ptr(pe), pe_group, pe_T)
+
+    def conv3x3(self, xpad, wname, h, w, Cin, Cout, *, bias=None, **kw):
+        """3x3 s1 p1 conv over a padded map as a 9-tap GEMM (M runs over the padded grid)."""
+        M = self.BT * (h + 2) * (w + 2)
+        return self.gemm(xpad, self.pw.w[wname], M, Cout, Cin, taps=9, geo=(self.BT, h, w), m_padded=1, bias=bias, **kw)
+
+    # ------------------------------------------------------------------ the network
+    def _build(self, skip_tmp_block):
+        pw, W_ = self.pw, self.pw.w
+        BT, ph, pwid, D = self.BT, self.ph, self.pw_, pw.D
+        P = ph * pwid
+        ntok = P + 1
+        M = BT * ntok
+        lib = self._lib
+        self.x_in = torch.empty((BT, 3, self.H, self.W), dtype=torch.float32, device=self.device)
+
+        # ---- position embedding for this resolution (dinov2.py:179-210): identity at 518x518, else bicubic
+        if P == 37 * 37 and self.H == self.W:
+            pos = W_["pos"]
+        else:
+            pos = torch.empty((ntok, D), dtype=torch.float32, device=self.device)
+            check = L.check
+            check(lib.vda_pos_embed_bicubic(W_["pos"].data_ptr(), pos.data_ptr(), D, 37, ph, pwid,
+                                            (ph + 0.1) / 37.0, (pwid + 0.1) / 37.0, L.stream_ptr()), "vda_pos_embed_bicubic")
+        self.bufs["pos"] = pos
+
+        # ---- patch embed (patch_embed.py:76-78) + cls + pos (dinov2.py:212-221)
+        a_pe = self.buf("im2col", BT * P, KPAD_PATCH)
+        resid = self.buf("resid", M, D, torch.float32)
+        self.op(lib.vda_im2col_patch, self.x_in.data_ptr(), a_pe.data_ptr(), self.dcode, BT, self.H, self.W, KPAD_PATCH)
+        self.op(lib.vda_cls_rows, resid.data_ptr(), W_["cls"].data_ptr(), pos.data_ptr(), BT, ntok, D)
+        self.gemm(a_pe, W_["patch.w"], BT * P, D, KPAD_PATCH, geo=(BT, ph, pwid), bias=W_["patch.b"], resid=resid, pos=pos,
+                  resid_map=L.MAP_TOKENS, resid_assign=1, pos_rows=ntok)
+        if "tokens0" in self.keep:
+            self.bufs["tokens0"] = resid
+
+        # ---- transformer blocks (block.py:83-87,105-106)
+        y = self.buf("y", M, D)
+        qkv = self.buf("qkv", M, 3 * D)
+        att = self.buf("att", M, D)
+        hid = self.buf("hid", M, 4 * D)
+        taps = []
+        for i in range(pw.depth):
+            self.layernorm(resid, y, W_[f"b{i}.norm1.w"], W_[f"b{i}.norm1.b"], 1e-6, M, D)
+            self.gemm(y, W_[f"b{i}.qkv.w"], M, 3 * D, D, bias=W_[f"b{i}.qkv.b"], out=qkv)
+            self.op(lib.vda_attention, qkv.data_ptr(), att.data_ptr(), self.dcode, BT, ntok, pw.heads, int(self.bf16),
+                    int(self.use_tc))
+            self.gemm(att, W_[f"b{i}.proj.w"], M, D, D, bias=W_[f"b{i}.proj.b"], resid=resid, gamma=W_[f"b{i}.ls1"])
+            self.layernorm(resid, y, W_[f"b{i}.norm2.w"], W_[f"b{i}.norm2.b"], 1e-6, M, D)
+            self.gemm(y, W_[f"b{i}.fc1.w"], M, 4 * D, D, bias=W_[f"b{i}.fc1.b"], act=L.ACT_GELU, out=hid)
+            self.gemm(hid, W_[f"b{i}.fc2.w"], M, D, 4 * D, bias=W_[f"b{i}.fc2.b"], resid=resid, gamma=W_[f"b{i}.ls2"])
+            if i in pw.taps:
+                t = self.buf(f"tap{len(taps)}", BT * P, D)
+                # final norm on the tap, class token dropped (dinov2.py:309-312)
+                self.layernorm(resid, t, W_["norm.w"], W_["norm.b"], 1e-6, M, D, group_rows=ntok, skip_first=1)
+                taps.append(t)
+        self._build_head(taps, skip_tmp_block)
+
+    # ------------------------------------------------------------------ motion module (motion_module.py:108-133,173-186)
+    def _motion_module(self, m, x, hw_geo, C, out, out_map):
+        """x: dense tokens [BT*h*w, C] (also the residual).  out: dense or padded buffer receiving proj_out(h) + x."""
+        pw, W_, lib = self.pw, self.pw.w, self._lib
+        h_, w_ = hw_geo
+        hw = h_ * w_
+        M = self.BT * hw
+        geo = (self.BT, h_, w_)
+        n = f"mm{m}"
+        g = self.buf(n + ".g", M, C)
+        hbuf = self.buf(n + ".h", M, C)
+        nbuf = self.buf(n + ".n", M, C)
+        qkv = self.buf(n + ".qkv", M, 3 * C)
+        att = self.buf(n + ".att", M, C)
+        ff = self.buf(n + ".ff", M, 4 * C)
+        stats = torch.empty((self.BT * 32 * 2,), dtype=torch.float64, device=self.device)
+        self.bufs[n + ".stats"] = stats
+        self.op(lib.vda_groupnorm_tokens, x.data_ptr(), self.dcode, g.data_ptr(), self.dcode, W_[n + ".gn.w"].data_ptr(),
+                W_[n + ".gn.b"].data_ptr(), 1e-6, self.BT, hw, C, 32, stats.data_ptr(), launches=3)
+        self.gemm(g, W_[n + ".in.w"], M, C, C, bias=W_[n + ".in.b"], out=hbuf)
+        for a in (0, 1):
+            self.layernorm(hbuf, nbuf, W_[f"{n}.a{a}.ln.w"], W_[f"{n}.a{a}.ln.b"], 1e-5, M, C, pe=W_[f"{n}.a{a}.pe"],
+                           pe_group=hw, pe_T=self.T)
+            self.gemm(nbuf, W_[f"{n}.a{a}.qkv.w"], M, 3 * C, C, out=qkv)
+            self.op(lib.vda_temporal_attention, qkv.data_ptr(), att.data_ptr(), self.dcode, self.batch, self.T, hw, C, 8,
+                    int(self.bf16))
+            self.gemm(att, W_[f"{n}.a{a}.out.w"], M, C, C, bias=W_[f"{n}.a{a}.out.b"], out=hbuf, res=hbuf)
+        self.layernorm(hbuf, nbuf, W_[n + ".ffln.w"], W_[n + ".ffln.b"], 1e-5, M, C)
+        self.gemm(nbuf, W_[n + ".ff1.w"], M, 8 * C, C, bias=W_[n + ".ff1.b"], act=L.ACT_GEGLU, out=ff)
+        self.gemm(ff, W_[n + ".ff2.w"], M, C, 4 * C, bias=W_[n + ".ff2.b"], out=hbuf, res=hbuf)
+        self.gemm(hbuf, W_[n + ".po.w"], M, C, C, geo=geo, bias=W_[n + ".po.b"], out=out, out_map=out_map, res=x,
+                  res_map=L.MAP_SAME)
+        if n in self.keep:
+            self.bufs[n] = out
+
+    # ------------------------------------------------------------------ fusion blocks (util/blocks.py:68-91,135-162)
+    def _rcu(self, name, x, x_relu, h, w, F, out, out_relu=None, res2=None):
+        """out = conv2(relu(conv1(relu(x)))) + x (+ res2); all maps padded at (h, w)."""
+        W_ = self.pw.w
+        t = self.padded(name + ".t", h, w, F)
+        self.conv3x3(x_relu, name + ".c1.w", h, w, F, F, bias=W_[name + ".c1.b"], act=L.ACT_RELU, out=t)
+        self.conv3x3(t, name + ".c2.w", h, w, F, F, bias=W_[name + ".c2.b"], out=out, out_relu=out_relu, res=x, res2=res2)
+
+    def _fusion(self, i, x0, x0_relu, x1, x1_relu, h, w, oh, ow, out, out_map):
+        """refinenet{i}: x0 (+ RCU1(x1)) -> RCU2 -> bilinear to (oh, ow) -> out_conv.  x0/x1 padded at (h, w)."""
+        W_, F = self.pw.w, self.pw.features
+        n = f"ref{i}"
+        if x1 is not None:
+            s = self.padded(n + ".s", h, w, F)
+            s_relu = self.padded(n + ".s_relu", h, w, F)
+            self._rcu(n + ".rcu1", x1, x1_relu, h, w, F, s, out_relu=s_relu, res2=x0)
+        else:
+            s, s_relu = x0, x0_relu
+        r = self.padded(n + ".r", h, w, F)
+        self._rcu(n + ".rcu2", s, s_relu, h, w, F, r)
+        u = self.buf(n + ".u", self.BT * oh * ow, F)
+        self.op(self._lib.vda_bilinear, r.data_ptr(), u.data_ptr(), self.dcode, self.BT, h, w, 1, oh, ow, 0, F)
+        self.gemm(u, W_[n + ".out.w"], self.BT * oh * ow, F, F, geo=(self.BT, oh, ow), bias=W_[n + ".out.b"], out=out,
+                  out_map=out_map)
+
+    # ------------------------------------------------------------------ DPTHeadTemporal.forward (dpt_temporal.py:53-99)
+    def _build_head(self, taps, skip_tmp_block):
+        pw, W_, lib = self.pw, self.pw.w, self._lib
+        BT, ph, pwid, D, F, oc = self.BT, self.ph, self.pw_, pw.D, pw.features, pw.oc
+        P = ph * pwid
+        geo3 = (BT, ph, pwid)
+        h1, w1, h2, w2, h3, w3 = 4 * ph, 4 * pwid, 2 * ph, 2 * pwid, ph, pwid
+        h4, w4 = (ph + 1) // 2, (pwid + 1) // 2
+        # reassemble: projects (1x1) + resize layers (dpt.py:50-90)
+        t0 = self.buf("t0", BT * P, oc[0])
+        self.gemm(taps[0], W_["proj0.w"], BT * P, oc[0], D, bias=W_["proj0.b"], out=t0)
+        l1 = self.padded("layer_1", h1, w1, oc[0])
+        self.gemm(t0, W_["rs0.w"], BT * P, 16 * oc[0], oc[0], geo=geo3, bias=W_["rs0.b"], out=l1, out_map=L.MAP_CONVT, ct_k=4,
+                  ct_cout=oc[0])
+        t1 = self.buf("t1", BT * P, oc[1])
+        self.gemm(taps[1], W_["proj1.w"], BT * P, oc[1], D, bias=W_["proj1.b"], out=t1)
+        l2 = self.padded("layer_2", h2, w2, oc[1])
+        self.gemm(t1, W_["rs1.w"], BT * P, 4 * oc[1], oc[1], geo=geo3, bias=W_["rs1.b"], out=l2, out_map=L.MAP_CONVT, ct_k=2,
+                  ct_cout=oc[1])
+        l3 = self.buf("layer_3", BT * P, oc[2])
+        self.gemm(taps[2], W_["proj2.w"], BT * P, oc[2], D, bias=W_["proj2.b"], out=l3)
+        t3 = self.padded("t3", h3, w3, oc[3])
+        self.gemm(taps[3], W_["proj3.w"], BT * P, oc[3], D, geo=geo3, bias=W_["proj3.b"], out=t3, out_map=L.MAP_PADDED)
+        l4 = self.buf("layer_4", BT * h4 * w4, oc[3])
+        self.conv3x3(t3, "rs3.w", h3, w3, oc[3], oc[3], bias=W_["rs3.b"], out=l4, out_map=L.MAP_STRIDE2)
+        # motion modules 0/1 on layer_3 / layer_4 (dpt_temporal.py:75-76)
+        l3m = self.padded("mm0", h3, w3, oc[2])
+        self._motion_module(0, l3, (h3, w3), oc[2], l3m, L.MAP_PADDED)
+        l4m = self.padded("mm1", h4, w4, oc[3])
+        self._motion_module(1, l4, (h4, w4), oc[3], l4m, L.MAP_PADDED)
+        # layerN_rn (3x3, no bias), raw + relu copies (dpt_temporal.py:78-81)
+        rn, rn_relu = {}, {}
+        for i, (src, h, w) in enumerate(((l1, h1, w1), (l2, h2, w2), (l3m, h3, w3), (l4m, h4, w4)), start=1):
+            rn[i] = self.padded(f"l{i}r", h, w, F)
+            rn_relu[i] = self.padded(f"l{i}r_relu", h, w, F)
+            self.conv3x3(src, f"rn{i}.w", h, w, oc[i - 1], F, out=rn[i], out_relu=rn_relu[i])
+        # refinenet4 (+ motion module 2) (dpt_temporal.py:83-85)
+        if skip_tmp_block:
+            p4 = self.padded("path_4", h3, w3, F)
+            self._fusion(4, rn[4], rn_relu[4], None, None, h4, w4, h3, w3, p4, L.MAP_PADDED)
+        else:
+            p4d = self.buf("path_4d", BT * h3 * w3, F)
+            self._fusion(4, rn[4], rn_relu[4], None, None, h4, w4, h3, w3, p4d, L.MAP_SAME)
+            p4 = self.padded("path_4", h3, w3, F)
+            self._motion_module(2, p4d, (h3, w3), F, p4, L.MAP_PADDED)
+        # refinenet3 + motion module 3 (dpt_temporal.py:86-87)
+        p3d = self.buf("path_3d", BT * h2 * w2, F)
+        self._fusion(3, p4, None, rn[3], rn_relu[3], h3, w3, h2, w2, p3d, L.MAP_SAME)
+        p3 = self.padded("path_3", h2, w2, F)
+        self._motion_module(3, p3d, (h2, w2), F, p3, L.MAP_PADDED)
+        # refinenet2, refinenet1 (dpt_temporal.py:88-89)
+        p2 = self.padded("path_2", h1, w1, F)
+        self._fusion(2, p3, None, rn[2], rn_relu[2], h2, w2, h1, w1, p2, L.MAP_PADDED)
+        h0, w0 = 2 * h1, 2 * w1
+        p1 = self.padded("path_1", h0, w0, F)
+        self._fusion(1, p2, None, rn[1], rn_relu[1], h1, w1, h0, w0, p1, L.MAP_PADDED)
+        # output_conv1 -> bilinear to (14ph, 14pw) -> fp32 island output_conv2 (dpt_temporal.py:91-99)
+        o1 = self.buf("oc1", BT * h0 * w0, F // 2)
+        self.conv3x3(p1, "oc1.w", h0, w0, F, F // 2, bias=W_["oc1.b"], out=o1, out_map=L.MAP_DENSE)
+        up = self.padded("up", self.H, self.W, F // 2)
+        self.op(lib.vda_bilinear, o1.data_ptr(), up.data_ptr(), self.dcode, BT, h0, w0, 0, self.H, self.W, 1, F // 2)
+        depth = torch.empty((BT, self.H, self.W), dtype=self.adt, device=self.device)
+        self.bufs["depth"] = depth
+        Mup = BT * (self.H + 2) * (self.W + 2)
+        if self.use_tc:
+            self.gemm(up, W_["oc2.whl"], Mup, 32, F // 2, taps=9, ksplit=2, geo=(BT, self.H, self.W), m_padded=1,
+                      bias=W_["oc2.b"], out_map=L.MAP_DENSE, head_w=W_["oc2.hw"], head_out=depth, head_b=pw.head_b)
+        else:
+            self.gemm(up, W_["oc2.w32"], Mup, 32, F // 2, taps=9, geo=(BT, self.H, self.W), m_padded=1, bias=W_["oc2.b"],
+                      out_map=L.MAP_DENSE, head_w=W_["oc2.hw"], head_out=depth, head_b=pw.head_b)
+        self.depth = depth
+
+    # ------------------------------------------------------------------ execution
+    def run(self, x: torch.Tensor) -> torch.Tensor:
+        """x: [BT,3,H,W] fp32 on this plan's device.  Returns the plan-owned depth buffer [BT,H,W]."""
+        self.x_in.copy_(x.reshape(self.x_in.shape), non_blocking=True)
+        self.launch()
+        return self.depth
+
+    def launch(self):
+        st = L.stream_ptr()
+        lib = self._lib
+        gemm = lib.vda_gemm
+        for fn, args in self.ops:
+            if fn is gemm:
+                rc = fn(C.byref(args[0]), st)
+            else:
+                rc = fn(*args, st)
+            if rc != 0:
+                raise L.VdaError(f"{fn.__name__} failed (rc={rc}): {lib.vda_last_error().decode(errors='replace')}")
