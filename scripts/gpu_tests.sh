@@ -1,0 +1,17 @@
+#!/usr/bin/env bash
+# Runs the GPU test files one process per group (a faulting kernel poisons its CUDA context), logs to gpurun_out/.
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
+run() { # name, timeout, pytest args...
+  local name=$1 to=$2; shift 2
+  timeout "$to" python -m pytest "$@" -q -s -m gpu -p no:cacheprovider > "gpurun_out/$name.log" 2>&1
+  echo "== $name rc=$? $(tail -1 gpurun_out/$name.log)"
+}
+run kernels 600 tests/test_gpu_kernels.py
+run tc_gemm 300 tests/test_gpu_tc.py::test_gemm_tc_bias
+run tc_epi 300 tests/test_gpu_tc.py::test_gemm_tc_epilogues
+run tc_conv 300 tests/test_gpu_tc.py::test_conv3x3_tc tests/test_gpu_tc.py::test_output_head_tc_hi_lo_split
+run tc_attn 300 tests/test_gpu_tc.py::test_flash_attention_tc
+run fwd_fp32 900 tests/test_gpu_forward.py -k "fp32 or taps or contract"
+run fwd_bf16 900 tests/test_gpu_forward.py -k "bf16"

@@ -1,0 +1,150 @@
+"""GPU parity tests of the tcgen05 / TMEM / TMA kernels (GEMM + conv-as-GEMM with fused epilogues, flash
+attention) through the C ABI, against fp32 PyTorch references with the same bf16 rounding points."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from tests.test_gpu_kernels import R, _lib, _pad_nhwc, _unpad, dev, run_gemm
+from tests.util import bf16_close, stats
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (300, 256, 128), (1000, 64, 192), (777, 48, 384), (4500, 3072, 1024),
+                                   (20000, 1024, 4096), (260, 32, 64), (129, 384, 1152)])
+def test_gemm_tc_bias(M, N, K):
+    L, lib = _lib()
+    torch.manual_seed(M + N + K)
+    A = torch.randn(M, K, device=dev).bfloat16()
+    B = (torch.randn(N, K, device=dev) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device=dev)
+    out = torch.full((M, N), float("nan"), device=dev, dtype=torch.bfloat16)
+    run_gemm(L, lib, A=A, B=B, lda=K, ldb=K, rowsA=M, a_dtype=L.BF16, b_dtype=L.BF16, M=M, N=N, K=K, taps=1, ksplit=1, bias=bias,
+             round_bf16=1, out_dtype=L.BF16, out=out, ldo=N, use_tc=1)
+    ref = R(A.float() @ B.float().T + bias)
+    bf16_close(f"gemm_tc_{M}x{N}x{K}", out.float(), ref)
+
+
+def test_gemm_tc_epilogues():
+    from video_depth_anything_b200.engine import _convt_pack, _geglu_interleave
+    L, lib = _lib()
+    torch.manual_seed(11)
+    M, K, N = 1500, 256, 512
+    A = torch.randn(M, K, device=dev).bfloat16()
+    Wt = (torch.randn(N, K, device=dev) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device=dev)
+    base = dict(A=A, lda=K, ldb=K, rowsA=M, a_dtype=L.BF16, b_dtype=L.BF16, M=M, K=K, taps=1, ksplit=1, round_bf16=1,
+                out_dtype=L.BF16, use_tc=1)
+    lin = R(A.float() @ Wt.float().T + bias)
+    # GELU (mlp.py:37-38 under autocast: bf16 linear output, bf16 gelu output)
+    out = torch.zeros(M, N, device=dev, dtype=torch.bfloat16)
+    run_gemm(L, lib, B=Wt, N=N, bias=bias, act=L.ACT_GELU, out=out, ldo=N, **base)
+    bf16_close("tc_gelu", out.float(), R(F.gelu(lin)))
+    # LayerScale + fp32 residual (block.py:105-106)
+    gam = torch.rand(N, device=dev) + 0.5
+    resid = torch.randn(M, N, device=dev)
+    r0 = resid.clone()
+    run_gemm(L, lib, B=Wt, N=N, bias=bias, resid=resid, gamma=gam, ldresid=N, **base)
+    s = stats("tc_resid", resid, r0 + lin * gam)
+    assert s["max_rel_to_peak"] < 2e-2 and s["mean_abs"] < 2e-3
+    # bf16 residual in place + relu copy
+    res = torch.randn(M, N, device=dev).bfloat16()
+    o2 = res.clone()
+    orl = torch.zeros_like(o2)
+    run_gemm(L, lib, B=Wt, N=N, bias=bias, out=o2, out_relu=orl, ldo=N, res=o2, ldres=N, **base)
+    bf16_close("tc_res_inplace", o2.float(), R(lin + res.float()))
+    assert torch.equal(orl, torch.relu(o2))
+    # GEGLU
+    Wg = (torch.randn(2 * N, K, device=dev) / K ** 0.5).bfloat16()
+    bg = torch.randn(2 * N, device=dev)
+    og = torch.zeros(M, N, device=dev, dtype=torch.bfloat16)
+    run_gemm(L, lib, B=_geglu_interleave(Wg), N=2 * N, bias=_geglu_interleave(bg), act=L.ACT_GEGLU, out=og, ldo=N, **base)
+    v, g = R(A.float() @ Wg.float().T + bg).chunk(2, -1)
+    bf16_close("tc_geglu", og.float(), R(v * R(F.gelu(g))))
+    # conv-transpose k=2 scatter into a padded map
+    Bf, H, W_, Ci, Co, k = 3, 9, 11, 96, 96, 2
+    x = torch.randn(Bf, Ci, H, W_, device=dev).bfloat16()
+    w = (torch.randn(Ci, Co, k, k, device=dev) * 0.1).bfloat16()
+    b = torch.randn(Co, device=dev)
+    xd = x.permute(0, 2, 3, 1).reshape(-1, Ci).contiguous()
+    out = torch.zeros(Bf * (H * k + 2) * (W_ * k + 2), Co, device=dev, dtype=torch.bfloat16)
+    run_gemm(L, lib, A=xd, B=_convt_pack(w), lda=Ci, ldb=Ci, rowsA=xd.shape[0], a_dtype=L.BF16, b_dtype=L.BF16, M=xd.shape[0],
+             N=k * k * Co, K=Ci, taps=1, ksplit=1, gb=Bf, gh=H, gw=W_, bias=b, round_bf16=1, out_dtype=L.BF16, out=out, ldo=Co,
+             out_map=L.MAP_CONVT, ct_k=k, ct_cout=Co, use_tc=1)
+    ref = R(F.conv_transpose2d(x.float(), w.float(), b, stride=k))
+    bf16_close("tc_convt", _unpad(out, Bf, H * k, W_ * k).float(), ref)
+
+
+@pytest.mark.parametrize("Ci,Co,H,W", [(64, 64, 12, 10), (48, 64, 20, 17), (256, 128, 30, 30), (1024, 256, 19, 19)])
+def test_conv3x3_tc(Ci, Co, H, W):
+    from video_depth_anything_b200.engine import _conv3x3_pack
+    L, lib = _lib()
+    torch.manual_seed(Ci + Co)
+    Bf = 3
+    x = torch.randn(Bf, Ci, H, W, device=dev).bfloat16()
+    w = (torch.randn(Co, Ci, 3, 3, device=dev) / (9 * Ci) ** 0.5).bfloat16()
+    b = torch.randn(Co, device=dev)
+    skip = torch.randn(Bf, Co, H, W, device=dev).bfloat16()
+    xp, sp = _pad_nhwc(x), _pad_nhwc(skip)
+    Mp = xp.shape[0]
+    out = torch.zeros(Mp, Co, device=dev, dtype=torch.bfloat16)
+    common = dict(A=xp, B=_conv3x3_pack(w), lda=Ci, ldb=9 * Ci, rowsA=Mp, a_dtype=L.BF16, b_dtype=L.BF16, M=Mp, N=Co, K=Ci, taps=9,
+                  ksplit=1, gb=Bf, gh=H, gw=W, m_padded=1, bias=b, round_bf16=1, out_dtype=L.BF16, ldo=Co, use_tc=1)
+    run_gemm(L, lib, out=out, res=sp, ldres=Co, **common)
+    conv = R(F.conv2d(x.float(), w.float(), b, padding=1))
+    bf16_close(f"tc_conv_{Ci}_{Co}", _unpad(out, Bf, H, W).float(), R(conv + skip.float()))
+    g = out.reshape(Bf, H + 2, W + 2, Co)
+    assert float(g[:, 0].abs().max()) == 0 and float(g[:, :, -1].abs().max()) == 0
+    H2, W2 = (H + 1) // 2, (W + 1) // 2
+    outs = torch.zeros(Bf * H2 * W2, Co, device=dev, dtype=torch.bfloat16)
+    run_gemm(L, lib, out=outs, out_map=L.MAP_STRIDE2, **common)
+    ref2 = R(F.conv2d(x.float(), w.float(), b, stride=2, padding=1))
+    bf16_close(f"tc_conv_s2_{Ci}_{Co}", outs.reshape(Bf, H2, W2, Co).permute(0, 3, 1, 2).float(), ref2)
+
+
+def test_output_head_tc_hi_lo_split():
+    """output_conv2 (dpt.py:118-124): fp32 weights as bf16 hi+lo along K, fused ReLU -> 1x1 -> ReLU, bf16 result."""
+    from video_depth_anything_b200.engine import _conv3x3_pack
+    L, lib = _lib()
+    torch.manual_seed(12)
+    Bf, Ci, H, W = 2, 64, 28, 42
+    x = torch.randn(Bf, Ci, H, W, device=dev).bfloat16()
+    w = torch.randn(32, Ci, 3, 3, device=dev) / (9 * Ci) ** 0.5
+    b, hw_, hb = torch.randn(32, device=dev) * 0.1, torch.randn(32, device=dev).abs(), 0.05
+    wp = _conv3x3_pack(w)
+    hi = wp.bfloat16()
+    lo = (wp - hi.float()).bfloat16()
+    xp = _pad_nhwc(x)
+    Mp = xp.shape[0]
+    ho = torch.zeros(Bf * H * W, device=dev, dtype=torch.bfloat16)
+    run_gemm(L, lib, A=xp, B=torch.cat([hi, lo], 1).contiguous(), lda=Ci, ldb=18 * Ci, rowsA=Mp, a_dtype=L.BF16, b_dtype=L.BF16,
+             M=Mp, N=32, K=Ci, taps=9, ksplit=2, gb=Bf, gh=H, gw=W, m_padded=1, bias=b, round_bf16=1, out_dtype=L.BF16,
+             out_map=L.MAP_DENSE, head_w=hw_, head_out=ho, head_b=hb, use_tc=1)
+    ref = F.relu(F.conv2d(F.relu(F.conv2d(x.float(), w, b, padding=1)), hw_.reshape(1, 32, 1, 1), torch.tensor([hb], device=dev)))
+    bf16_close("tc_head", ho.float().reshape(Bf, 1, H, W), R(ref), ulps=1.01, frac=2e-3)
+
+
+@pytest.mark.parametrize("frames,ntok,heads", [(1, 128, 1), (2, 150, 3), (2, 1370, 6), (1, 2443, 2)])
+def test_flash_attention_tc(frames, ntok, heads):
+    L, lib = _lib()
+    torch.manual_seed(ntok)
+    st = L.stream_ptr()
+    D = heads * 64
+    qkv = (torch.randn(frames * ntok, 3 * D, device=dev) * 1.3).bfloat16()
+    o = torch.full((frames * ntok, D), float("nan"), device=dev, dtype=torch.bfloat16)
+    L.check(lib.vda_attention(qkv.data_ptr(), o.data_ptr(), L.BF16, frames, ntok, heads, 1, 1, st), "attn_tc")
+    torch.cuda.synchronize()
+    q, k, v = qkv.float().reshape(frames, ntok, 3, heads, 64).permute(2, 0, 3, 1, 4)
+    s = R((q * 0.125) @ k.transpose(-1, -2))
+    ref = R(R(s.softmax(-1)) @ v)
+    got = o.float().reshape(frames, ntok, heads, 64).permute(0, 2, 1, 3)
+    # the flash kernel rounds un-normalised probabilities (exp(s - running max)) instead of softmax outputs:
+    # an uncorrelated bf16 rounding of P, averaged over the keys -- well inside 2 output ulps
+    bf16_close(f"flash_tc_{ntok}", got, ref, ulps=2.0, frac=2e-2)
+    exact = s.softmax(-1) @ v
+    s2 = stats(f"flash_tc_vs_exact_{ntok}", got, exact)
+    assert s2["mean_abs"] < 4e-3 * s2["ref_peak"]
+    # and it must agree with the SIMT kernel that follows the reference's rounding exactly
+    o2 = torch.zeros_like(o)
+    L.check(lib.vda_attention(qkv.data_ptr(), o2.data_ptr(), L.BF16, frames, ntok, heads, 1, 0, st), "attn_simt")
+    bf16_close(f"flash_tc_vs_simt_{ntok}", o.float(), o2.float(), ulps=2.0, frac=2e-2)
