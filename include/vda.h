@@ -98,9 +98,9 @@ typedef struct vda_gemm_desc {
   int32_t resid_map;
   int32_t resid_assign;
   int32_t pos_rows;
-  /* fused output tail (dpt.py:119-123): d = relu(sum_n relu(acc+bias)[n]*head_w[n] + head_b); head_out[row] = R(d) */
+  /* fused output tail (dpt.py:119-123): d = relu(sum_n relu(acc+bias)[n]*head_w[n] + head_b); head_out[row] = d (fp32, never rounded) */
   const float* head_w;
-  void* head_out;    /* [rows] of out_dtype                                                          */
+  void* head_out;    /* [rows] fp32 (the island runs outside autocast, dpt_temporal.py:95-97)        */
   float head_b;
   /* ---- execution ---- */
   int32_t use_tc;    /* 1: tcgen05/TMEM/TMA kernel (bf16 operands); 0: SIMT fp32-accumulate kernel   */
@@ -124,7 +124,7 @@ int vda_layernorm(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, cons
                   const float* pe, int32_t pe_group, int32_t pe_T, vda_stream_t stream);
 
 /* GroupNorm(groups, C, eps) per frame over dense tokens x[frames, hw, C] (motion_module.py:89,116) -> y tokens.
- * stats: scratch of frames*groups*2 doubles. */
+ * stats: scratch of frames*groups*2*33 doubles (mean/rstd + per-block partial sums; reduction is deterministic). */
 int vda_groupnorm_tokens(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, const float* w, const float* b,
                          float eps, int32_t frames, int32_t hw, int32_t C, int32_t groups, double* stats,
                          vda_stream_t stream);
@@ -139,9 +139,10 @@ int vda_attention(const void* qkv, void* o, int32_t dtype, int32_t frames, int32
 int vda_temporal_attention(const void* qkv, void* o, int32_t dtype, int32_t batch, int32_t T, int32_t hw, int32_t C,
                            int32_t heads, int32_t round_bf16, vda_stream_t stream);
 
-/* Bilinear resize, align_corners=True (blocks.py:156-158, dpt_temporal.py:92-94), channels-last. */
-int vda_bilinear(const void* in, void* out, int32_t dtype, int32_t frames, int32_t ih, int32_t iw, int32_t in_padded,
-                 int32_t oh, int32_t ow, int32_t out_padded, int32_t C, vda_stream_t stream);
+/* Bilinear resize, align_corners=True (blocks.py:156-158, dpt_temporal.py:92-94), channels-last.  Under CUDA autocast
+ * upsample_bilinear2d is an fp32 op: bf16 in -> fp32 out is the un-rounded form the output head consumes. */
+int vda_bilinear(const void* in, int32_t in_dtype, void* out, int32_t out_dtype, int32_t frames, int32_t ih, int32_t iw,
+                 int32_t in_padded, int32_t oh, int32_t ow, int32_t out_padded, int32_t C, vda_stream_t stream);
 
 /* Patch-embed im2col (patch_embed.py:76): x[frames,3,H,W] f32 -> A[frames*(H/14)*(W/14), kpad] (k = c*196+i*14+j; pad = 0). */
 int vda_im2col_patch(const float* x, void* A, int32_t a_dtype, int32_t frames, int32_t H, int32_t W, int32_t kpad,

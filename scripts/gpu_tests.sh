@@ -11,7 +11,10 @@ run() { # name, timeout, pytest args...
 run kernels 600 tests/test_gpu_kernels.py
 run tc_gemm 300 tests/test_gpu_tc.py::test_gemm_tc_bias
 run tc_epi 300 tests/test_gpu_tc.py::test_gemm_tc_epilogues
-run tc_conv 300 tests/test_gpu_tc.py::test_conv3x3_tc tests/test_gpu_tc.py::test_output_head_tc_hi_lo_split
+run tc_conv 300 tests/test_gpu_tc.py::test_conv3x3_tc tests/test_gpu_tc.py::test_output_head_tc_tf32
 run tc_attn 300 tests/test_gpu_tc.py::test_flash_attention_tc
-run fwd_fp32 900 tests/test_gpu_forward.py -k "fp32 or taps or contract"
-run fwd_bf16 900 tests/test_gpu_forward.py -k "bf16"
+run fwd_fp32 900 tests/test_gpu_forward.py -k "(fp32 or taps or contract) and not driver"
+run fwd_bf16 900 tests/test_gpu_forward.py -k "bf16 and not driver"
+run driver 600 tests/test_gpu_forward.py -k "driver"
+timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "== smoke rc=$? $(tail -1 gpurun_out/smoke.log)"
+timeout 900 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.log 2>&1; echo "== bench rc=$? $(tail -c 1500 gpurun_out/bench.log)"

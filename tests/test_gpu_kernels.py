@@ -188,7 +188,7 @@ def test_layernorm_groupnorm(mode):
         x = (torch.randn(frames, hw, C_, device=dev) * 1.5 + 0.3).to(dt)
         w, b = torch.rand(C_, device=dev) + 0.5, torch.randn(C_, device=dev)
         y = torch.zeros_like(x)
-        stt = torch.zeros(frames * 32 * 2, dtype=torch.float64, device=dev)
+        stt = torch.zeros(frames * 32 * 2 * 33, dtype=torch.float64, device=dev)
         L.check(lib.vda_groupnorm_tokens(x.data_ptr(), L.dt(x), y.data_ptr(), L.dt(y), w.data_ptr(), b.data_ptr(), 1e-6, frames, hw,
                                          C_, 32, stt.data_ptr(), st), "gn")
         ref = F.group_norm(x.float().permute(0, 2, 1), 32, w, b, 1e-6).permute(0, 2, 1)
@@ -209,7 +209,7 @@ def test_bilinear_im2col_misc(mode):
         x = torch.randn(Bf, Cc, ih, iw, device=dev).to(dt)
         xin = _pad_nhwc(x)
         out = torch.zeros(Bf * oh * ow, Cc, device=dev, dtype=dt)
-        L.check(lib.vda_bilinear(xin.data_ptr(), out.data_ptr(), L.dt(x), Bf, ih, iw, 1, oh, ow, 0, Cc, st), "bilinear")
+        L.check(lib.vda_bilinear(xin.data_ptr(), L.dt(x), out.data_ptr(), L.dt(x), Bf, ih, iw, 1, oh, ow, 0, Cc, st), "bilinear")
         ref = F.interpolate(x, size=(oh, ow), mode="bilinear", align_corners=True)
         got = out.reshape(Bf, oh, ow, Cc).permute(0, 3, 1, 2)
         if mode == "bf16":
@@ -218,8 +218,13 @@ def test_bilinear_im2col_misc(mode):
             assert stats(f"bilinear_{oh}x{ow}", got, ref)["max_rel_to_peak"] < 2e-6
         outp = torch.zeros(Bf * (oh + 2) * (ow + 2), Cc, device=dev, dtype=dt)
         xd = x.permute(0, 2, 3, 1).reshape(-1, Cc).contiguous()
-        L.check(lib.vda_bilinear(xd.data_ptr(), outp.data_ptr(), L.dt(x), Bf, ih, iw, 0, oh, ow, 1, Cc, st), "bilinear")
+        L.check(lib.vda_bilinear(xd.data_ptr(), L.dt(x), outp.data_ptr(), L.dt(x), Bf, ih, iw, 0, oh, ow, 1, Cc, st), "bilinear")
         assert torch.equal(_unpad(outp, Bf, oh, ow), got)
+        if mode == "bf16":  # bf16 in -> un-rounded fp32 out (what autocast's fp32 upsample produces)
+            o32 = torch.zeros(Bf * oh * ow, Cc, device=dev)
+            L.check(lib.vda_bilinear(xin.data_ptr(), L.BF16, o32.data_ptr(), L.F32, Bf, ih, iw, 1, oh, ow, 0, Cc, st), "bilinear")
+            assert stats("bilinear_bf16_f32", o32.reshape(Bf, oh, ow, Cc).permute(0, 3, 1, 2), F.interpolate(
+                x.float(), size=(oh, ow), mode="bilinear", align_corners=True))["max_rel_to_peak"] < 2e-6
     H, W = 28, 42
     x = torch.randn(3, 3, H, W, device=dev)
     A = torch.zeros(3 * 2 * 3, 640, device=dev, dtype=dt)

@@ -102,26 +102,27 @@ def test_conv3x3_tc(Ci, Co, H, W):
     bf16_close(f"tc_conv_s2_{Ci}_{Co}", outs.reshape(Bf, H2, W2, Co).permute(0, 3, 1, 2).float(), ref2)
 
 
-def test_output_head_tc_hi_lo_split():
-    """output_conv2 (dpt.py:118-124): fp32 weights as bf16 hi+lo along K, fused ReLU -> 1x1 -> ReLU, bf16 result."""
+def test_output_head_tc_tf32():
+    """output_conv2 (dpt.py:118-124) in the bf16 build: fp32 activations and weights through tcgen05 kind::tf32 (what
+    cuDNN does for an fp32 conv by default), fused ReLU -> 1x1 -> ReLU, fp32 result."""
     from video_depth_anything_b200.engine import _conv3x3_pack
     L, lib = _lib()
     torch.manual_seed(12)
-    Bf, Ci, H, W = 2, 64, 28, 42
-    x = torch.randn(Bf, Ci, H, W, device=dev).bfloat16()
-    w = torch.randn(32, Ci, 3, 3, device=dev) / (9 * Ci) ** 0.5
-    b, hw_, hb = torch.randn(32, device=dev) * 0.1, torch.randn(32, device=dev).abs(), 0.05
-    wp = _conv3x3_pack(w)
-    hi = wp.bfloat16()
-    lo = (wp - hi.float()).bfloat16()
-    xp = _pad_nhwc(x)
-    Mp = xp.shape[0]
-    ho = torch.zeros(Bf * H * W, device=dev, dtype=torch.bfloat16)
-    run_gemm(L, lib, A=xp, B=torch.cat([hi, lo], 1).contiguous(), lda=Ci, ldb=18 * Ci, rowsA=Mp, a_dtype=L.BF16, b_dtype=L.BF16,
-             M=Mp, N=32, K=Ci, taps=9, ksplit=2, gb=Bf, gh=H, gw=W, m_padded=1, bias=b, round_bf16=1, out_dtype=L.BF16,
-             out_map=L.MAP_DENSE, head_w=hw_, head_out=ho, head_b=hb, use_tc=1)
-    ref = F.relu(F.conv2d(F.relu(F.conv2d(x.float(), w, b, padding=1)), hw_.reshape(1, 32, 1, 1), torch.tensor([hb], device=dev)))
-    bf16_close("tc_head", ho.float().reshape(Bf, 1, H, W), R(ref), ulps=1.01, frac=2e-3)
+    for Ci in (32, 128):
+        Bf, H, W = 2, 28, 42
+        x = torch.randn(Bf, Ci, H, W, device=dev)
+        w = torch.randn(32, Ci, 3, 3, device=dev) / (9 * Ci) ** 0.5
+        b, hw_, hb = torch.randn(32, device=dev) * 0.1, torch.randn(32, device=dev).abs(), 0.05
+        xp = _pad_nhwc(x)
+        Mp = xp.shape[0]
+        ho = torch.zeros(Bf * H * W, device=dev)
+        run_gemm(L, lib, A=xp, B=_conv3x3_pack(w), lda=Ci, ldb=9 * Ci, rowsA=Mp, a_dtype=L.F32, b_dtype=L.F32, M=Mp, N=32, K=Ci,
+                 taps=9, ksplit=1, gb=Bf, gh=H, gw=W, m_padded=1, bias=b, round_bf16=1, out_dtype=L.BF16, out_map=L.MAP_DENSE,
+                 head_w=hw_, head_out=ho, head_b=hb, use_tc=1)
+        ref = F.relu(F.conv2d(F.relu(F.conv2d(x.double(), w.double(), b.double(), padding=1)), hw_.double().reshape(1, 32, 1, 1),
+                              torch.tensor([hb], device=dev, dtype=torch.float64)))
+        s = stats(f"tc_head_tf32_{Ci}", ho.reshape(Bf, 1, H, W), ref)
+        assert s["max_rel_to_peak"] < 2e-3 and s["mean_abs"] < 3e-4 * s["ref_peak"]  # tf32: 10-bit mantissa operands
 
 
 @pytest.mark.parametrize("frames,ntok,heads", [(1, 128, 1), (2, 150, 3), (2, 1370, 6), (1, 2443, 2)])
@@ -138,13 +139,17 @@ def test_flash_attention_tc(frames, ntok, heads):
     s = R((q * 0.125) @ k.transpose(-1, -2))
     ref = R(R(s.softmax(-1)) @ v)
     got = o.float().reshape(frames, ntok, heads, 64).permute(0, 2, 1, 3)
-    # the flash kernel rounds un-normalised probabilities (exp(s - running max)) instead of softmax outputs:
-    # an uncorrelated bf16 rounding of P, averaged over the keys -- well inside 2 output ulps
-    bf16_close(f"flash_tc_{ntok}", got, ref, ulps=2.0, frac=2e-2)
+    # The flash kernel rounds un-normalised probabilities exp(s - running max) to bf16 where the reference rounds the
+    # normalised softmax: two independent bf16 roundings of P.  So the gate is statistical: its error against exact
+    # fp32 attention must be of the same size as the reference's own bf16 error against exact attention.
     exact = s.softmax(-1) @ v
-    s2 = stats(f"flash_tc_vs_exact_{ntok}", got, exact)
-    assert s2["mean_abs"] < 4e-3 * s2["ref_peak"]
-    # and it must agree with the SIMT kernel that follows the reference's rounding exactly
+    e_ref = stats(f"ref_bf16_vs_exact_{ntok}", ref, exact)
+    e_got = stats(f"flash_tc_vs_exact_{ntok}", got, exact)
+    assert e_got["mean_abs"] <= 1.5 * e_ref["mean_abs"] and e_got["max_abs"] <= 3.0 * e_ref["max_abs"]
+    d = stats(f"flash_tc_vs_ref_{ntok}", got, ref)
+    assert d["mean_abs"] <= 2.0 * e_ref["mean_abs"] and d["max_abs"] <= 4.0 * e_ref["max_abs"]
+    # and it must agree equally well with the SIMT kernel that follows the reference's rounding exactly
     o2 = torch.zeros_like(o)
     L.check(lib.vda_attention(qkv.data_ptr(), o2.data_ptr(), L.BF16, frames, ntok, heads, 1, 0, st), "attn_simt")
-    bf16_close(f"flash_tc_vs_simt_{ntok}", o.float(), o2.float(), ulps=2.0, frac=2e-2)
+    d2 = stats(f"flash_tc_vs_simt_{ntok}", o.float(), o2.float())
+    assert d2["mean_abs"] <= 2.0 * e_ref["mean_abs"]

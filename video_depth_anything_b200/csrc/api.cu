@@ -49,7 +49,7 @@ static EncodeTiledFn get_encode() {
 }
 
 int vda_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t cols, uint64_t rows, uint64_t pitch_bytes,
-                     uint32_t box_cols, uint32_t box_rows) {
+                     uint32_t box_cols, uint32_t box_rows, int elem_bytes) {
   EncodeTiledFn enc = get_encode();
   if (!enc) {
     vda_set_error("cuTensorMapEncodeTiled is unavailable (driver too old?)");
@@ -59,7 +59,7 @@ int vda_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t cols, uint64_t
   cuuint64_t strides[1] = {pitch_bytes};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(out, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {

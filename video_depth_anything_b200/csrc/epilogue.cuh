@@ -120,7 +120,7 @@ __device__ __forceinline__ void epi_chunk(const Epi& e, const RowCtx& r, int n0,
 #pragma unroll
     for (int i = 0; i < 32; ++i) s = fmaf(fmaxf(v[i], 0.f), e.head_w[i], s);
     s = fmaxf(s + e.head_b, 0.f);
-    reinterpret_cast<TO*>(e.head_out)[r.out_row] = from_f32<TO>(s);
+    reinterpret_cast<float*>(e.head_out)[r.out_row] = s;  // fp32 island: never rounded
     return;
   }
   // ---- fp32 residual stream

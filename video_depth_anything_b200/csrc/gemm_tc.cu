@@ -31,7 +31,7 @@ struct TcArgs {
   int tiles_m, tiles_n;
 };
 
-template <int BN, typename TO, bool RB>
+template <int BN, typename TO, bool RB, bool TF32>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcArgs a,
                const Epi e) {
@@ -46,7 +46,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int kb_per_tap = (a.K + BK - 1) / BK;
+  constexpr int BKE = TF32 ? 32 : 64;  // elements per 128-byte K block
+  const int kb_per_tap = (a.K + BKE - 1) / BKE;
   const int num_kb = a.ksplit * a.taps * kb_per_tap;
   const int num_tiles = a.tiles_m * a.tiles_n;
 
@@ -87,8 +88,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
           uint8_t* sb = sa + C::A_BYTES;
           ptx::mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
-          ptx::tma_load_2d(sa, &tmA, kin * BK, m0 + off, &full[stage]);
-          ptx::tma_load_2d(sb, &tmB, st * a.K + kin * BK, n0, &full[stage]);
+          ptx::tma_load_2d(sa, &tmA, kin * BKE, m0 + off, &full[stage]);
+          ptx::tma_load_2d(sb, &tmB, st * a.K + kin * BKE, n0, &full[stage]);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -96,7 +97,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(BM, BN, 0, 0);
+      constexpr uint32_t idesc = TF32 ? ptx::make_idesc_tf32(BM, BN) : ptx::make_idesc_bf16(BM, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -114,8 +115,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint64_t db = ptx::make_sw128_desc(sb, 16, 1024);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in the (addr >> 4) field
-            ptx::mma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            // advance 32 B (16 bf16 / 8 tf32) inside the 128 B swizzle row: +2 in the (addr >> 4) field
+            if constexpr (TF32) ptx::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            else ptx::mma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           }
           ptx::tc_commit(&empty[stage]);
           if (kb == num_kb - 1) ptx::tc_commit(&tfull[acc]);
@@ -160,13 +162,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
-template <int BN>
+template <int BN, typename TO, bool RB, bool TF32>
 int launch_tc(const vda_gemm_desc* d, cudaStream_t st) {
   using C = TcCfg<BN>;
+  constexpr int EB = TF32 ? 4 : 2, BKE = 128 / EB;
   CUtensorMap tmA, tmB;
-  int rc = vda_make_tmap_2d(&tmA, d->A, (uint64_t)d->K, (uint64_t)d->rowsA, (uint64_t)d->lda * 2, BK, BM);
+  int rc = vda_make_tmap_2d(&tmA, d->A, (uint64_t)d->K, (uint64_t)d->rowsA, (uint64_t)d->lda * EB, BKE, BM, EB);
   if (rc) return rc;
-  rc = vda_make_tmap_2d(&tmB, d->B, (uint64_t)d->ksplit * d->taps * d->K, (uint64_t)d->N, (uint64_t)d->ldb * 2, BK, BN);
+  rc = vda_make_tmap_2d(&tmB, d->B, (uint64_t)d->ksplit * d->taps * d->K, (uint64_t)d->N, (uint64_t)d->ldb * EB, BKE, BN, EB);
   if (rc) return rc;
   TcArgs a;
   a.M = d->M; a.N = d->N; a.K = d->K; a.taps = d->taps; a.ksplit = d->ksplit; a.W2 = d->gw + 2;
@@ -175,7 +178,7 @@ int launch_tc(const vda_gemm_desc* d, cudaStream_t st) {
   const int tiles = a.tiles_m * a.tiles_n;
   const int grid = tiles < vda_sm_count() ? tiles : vda_sm_count();
   Epi e = make_epi(d);
-  auto kern = gemm_tc_kernel<BN, bf16, true>;
+  auto kern = gemm_tc_kernel<BN, TO, RB, TF32>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t ce = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
@@ -193,12 +196,19 @@ int launch_tc(const vda_gemm_desc* d, cudaStream_t st) {
 }  // namespace
 
 int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
-  VDA_CHECK_ARG(d->a_dtype == VDA_BF16 && d->b_dtype == VDA_BF16, "vda_gemm(tc): operands must be bf16");
+  const bool tf32 = d->a_dtype == VDA_F32 && d->b_dtype == VDA_F32;
+  VDA_CHECK_ARG(tf32 || (d->a_dtype == VDA_BF16 && d->b_dtype == VDA_BF16), "vda_gemm(tc): operands must be bf16/bf16 or f32/f32 (tf32)");
   VDA_CHECK_ARG(d->out_dtype == VDA_BF16 && d->round_bf16, "vda_gemm(tc): the tensor-core path is the bf16 build");
-  VDA_CHECK_ARG((d->lda % 8) == 0 && (d->ldb % 8) == 0, "vda_gemm(tc): lda/ldb must be multiples of 8 elements (TMA)");
+  const int al = tf32 ? 4 : 8;
+  VDA_CHECK_ARG((d->lda % al) == 0 && (d->ldb % al) == 0, "vda_gemm(tc): lda/ldb must be multiples of 16 bytes (TMA)");
   VDA_CHECK_ARG(((uintptr_t)d->A % 16) == 0 && ((uintptr_t)d->B % 16) == 0, "vda_gemm(tc): operands must be 16B aligned");
   VDA_CHECK_ARG(d->act != VDA_ACT_GEGLU || d->N % 64 == 0, "vda_gemm(tc): GEGLU needs N %% 64 == 0");
   VDA_CHECK_ARG(d->head_w == nullptr || d->N == 32, "vda_gemm(tc): fused head needs N == 32");
+  if (tf32) {
+    // the fp32 island of the bf16 build (dpt_temporal.py:95-97): fp32 operands through kind::tf32, as cuDNN does by default
+    VDA_CHECK_ARG(d->N <= 32, "vda_gemm(tc, tf32): only the N <= 32 output head is instantiated");
+    return launch_tc<32, bf16, true, true>(d, st);
+  }
   int bn;
   if (d->N <= 32) bn = 32;
   else if (d->N <= 64) bn = 64;
@@ -207,9 +217,9 @@ int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
   // small problems: prefer more tiles over wide tiles so every SM gets work
   if (bn == 256 && (int64_t)((d->M + 127) / 128) * ((d->N + 255) / 256) < vda_sm_count()) bn = 128;
   switch (bn) {
-    case 32: return launch_tc<32>(d, st);
-    case 64: return launch_tc<64>(d, st);
-    case 128: return launch_tc<128>(d, st);
-    default: return launch_tc<256>(d, st);
+    case 32: return launch_tc<32, bf16, true, false>(d, st);
+    case 64: return launch_tc<64, bf16, true, false>(d, st);
+    case 128: return launch_tc<128, bf16, true, false>(d, st);
+    default: return launch_tc<256, bf16, true, false>(d, st);
   }
 }

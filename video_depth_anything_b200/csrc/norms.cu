@@ -68,17 +68,18 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x
 }
 
 // ---------------------------------------------------------------- GroupNorm
-// pass 1: per (frame, group) sum and sum of squares (fp32 partials, fp64 atomics).
+// Deterministic three-step reduction (no atomics): per-block partial sums -> per (frame, group) mean / rstd -> apply.
+constexpr int GN_MAX_BLOCKS = 32;
+
 template <typename TI>
-__global__ void __launch_bounds__(256) gn_stats_kernel(const TI* __restrict__ x, double* __restrict__ stats, int hw, int C,
+__global__ void __launch_bounds__(256) gn_stats_kernel(const TI* __restrict__ x, double* __restrict__ partial, int hw, int C,
                                                       int groups, int rows_per_block) {
-  __shared__ float sh[64][2];
+  __shared__ float sh_s[256 * 8];
+  __shared__ float sh_q[256 * 8];
   const int f = blockIdx.y;
   const int nv = C >> 3;
   const int cv = threadIdx.x % nv, rsub = threadIdx.x / nv, rstep = blockDim.x / nv;
   const int cpg = C / groups;
-  for (int i = threadIdx.x; i < groups * 2; i += blockDim.x) (&sh[0][0])[i] = 0.f;
-  __syncthreads();
   float s[8] = {}, q[8] = {};
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(hw, r0 + rows_per_block);
@@ -92,25 +93,59 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(const TI* __restrict__ x,
         q[i] = fmaf(v[i], v[i], q[i]);
       }
     }
+  }
+  // sh[rsub][channel]; rows of inactive threads stay zero
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    sh_s[threadIdx.x * 8 + i] = 0.f;
+    sh_q[threadIdx.x * 8 + i] = 0.f;
+  }
+  __syncthreads();
+  if (rsub < rstep) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      int g = (cv * 8 + i) / cpg;
-      atomicAdd(&sh[g][0], s[i]);
-      atomicAdd(&sh[g][1], q[i]);
+      sh_s[rsub * C + cv * 8 + i] = s[i];
+      sh_q[rsub * C + cv * 8 + i] = q[i];
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < groups; i += blockDim.x) {
-    atomicAdd(&stats[((long long)f * groups + i) * 2 + 0], (double)sh[i][0]);
-    atomicAdd(&stats[((long long)f * groups + i) * 2 + 1], (double)sh[i][1]);
+  if (threadIdx.x < groups) {
+    const int g = threadIdx.x;
+    double ts = 0, tq = 0;
+    for (int rs = 0; rs < rstep; ++rs)
+      for (int c = g * cpg; c < (g + 1) * cpg; ++c) {
+        ts += (double)sh_s[rs * C + c];
+        tq += (double)sh_q[rs * C + c];
+      }
+    double* out = partial + (((long long)f * GN_MAX_BLOCKS + blockIdx.x) * groups + g) * 2;
+    out[0] = ts;
+    out[1] = tq;
   }
 }
 
-// pass 2: y = a*x + b' with a = rstd*w, b' = -a*mean + bias (the fused-parameter form ATen uses).
+__global__ void gn_finalize_kernel(const double* __restrict__ partial, double* __restrict__ stats, int nblocks, int groups,
+                                   double cnt, float eps, int total) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;  // (frame, group)
+  if (i >= total) return;
+  const int f = i / groups, g = i % groups;
+  double ts = 0, tq = 0;
+  for (int b = 0; b < nblocks; ++b) {
+    const double* p = partial + (((long long)f * GN_MAX_BLOCKS + b) * groups + g) * 2;
+    ts += p[0];
+    tq += p[1];
+  }
+  const double mean = ts / cnt;
+  double var = tq / cnt - mean * mean;
+  if (var < 0) var = 0;
+  stats[2 * i] = mean;
+  stats[2 * i + 1] = (double)rsqrtf((float)var + eps);
+}
+
+// y = a*x + b' with a = rstd*w, b' = -a*mean + bias (the fused-parameter form ATen uses).
 template <typename TI, typename TO, bool RB>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const TI* __restrict__ x, TO* __restrict__ y,
                                                       const double* __restrict__ stats, const float* __restrict__ w,
-                                                      const float* __restrict__ b, float eps, int hw, int C, int groups,
+                                                      const float* __restrict__ b, int hw, int C, int groups,
                                                       long long total_vec) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total_vec) return;
@@ -119,19 +154,15 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const TI* __restrict__ x,
   const long long row = idx / nv;
   const int f = (int)(row / hw);
   const int cpg = C / groups;
-  const double cnt = (double)hw * cpg;
   float v[8], o[8];
   Vec8<TI>::load(x + row * C + cv * 8, v);
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     int ch = cv * 8 + i, g = ch / cpg;
-    double su = stats[((long long)f * groups + g) * 2], sq = stats[((long long)f * groups + g) * 2 + 1];
-    double mean = su / cnt;
-    double var = sq / cnt - mean * mean;
-    if (var < 0) var = 0;
-    float rstd = rsqrtf((float)var + eps);
+    const float mean = (float)stats[((long long)f * groups + g) * 2];
+    const float rstd = (float)stats[((long long)f * groups + g) * 2 + 1];
     float a = rstd * w[ch];
-    float bb = -a * (float)mean + b[ch];
+    float bb = -a * mean + b[ch];
     o[i] = R<RB>(a * v[i] + bb);
   }
   Vec8<TO>::store(y + row * C + cv * 8, o);
@@ -167,23 +198,24 @@ extern "C" int vda_groupnorm_tokens(const void* x, int32_t x_dtype, void* y, int
                 C, groups);
   VDA_CHECK_ARG(x_dtype == y_dtype, "vda_groupnorm_tokens: x/y dtypes must match");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  cudaError_t ce = cudaMemsetAsync(stats, 0, sizeof(double) * 2 * frames * groups, st);
-  if (ce != cudaSuccess) {
-    vda_set_error("vda_groupnorm_tokens: memset failed: %s", cudaGetErrorString(ce));
-    return (int)ce;
-  }
   int blocks_per_frame = (hw + 255) / 256;
-  if (blocks_per_frame > 32) blocks_per_frame = 32;
+  if (blocks_per_frame > GN_MAX_BLOCKS) blocks_per_frame = GN_MAX_BLOCKS;
   const int rpb = (hw + blocks_per_frame - 1) / blocks_per_frame;
+  blocks_per_frame = (hw + rpb - 1) / rpb;
   dim3 g1(blocks_per_frame, frames);
+  double* partial = stats + (size_t)frames * groups * 2;  // [frames][GN_MAX_BLOCKS][groups][2]
   const long long total_vec = (long long)frames * hw * (C / 8);
   const unsigned g2 = (unsigned)((total_vec + 255) / 256);
+  const double cnt = (double)hw * (C / groups);
+  const int fg = frames * groups;
   if (x_dtype == VDA_BF16) {
-    gn_stats_kernel<bf16><<<g1, 256, 0, st>>>((const bf16*)x, stats, hw, C, groups, rpb);
-    gn_apply_kernel<bf16, bf16, true><<<g2, 256, 0, st>>>((const bf16*)x, (bf16*)y, stats, w, b, eps, hw, C, groups, total_vec);
+    gn_stats_kernel<bf16><<<g1, 256, 0, st>>>((const bf16*)x, partial, hw, C, groups, rpb);
+    gn_finalize_kernel<<<(fg + 127) / 128, 128, 0, st>>>(partial, stats, blocks_per_frame, groups, cnt, eps, fg);
+    gn_apply_kernel<bf16, bf16, true><<<g2, 256, 0, st>>>((const bf16*)x, (bf16*)y, stats, w, b, hw, C, groups, total_vec);
   } else {
-    gn_stats_kernel<float><<<g1, 256, 0, st>>>((const float*)x, stats, hw, C, groups, rpb);
-    gn_apply_kernel<float, float, false><<<g2, 256, 0, st>>>((const float*)x, (float*)y, stats, w, b, eps, hw, C, groups, total_vec);
+    gn_stats_kernel<float><<<g1, 256, 0, st>>>((const float*)x, partial, hw, C, groups, rpb);
+    gn_finalize_kernel<<<(fg + 127) / 128, 128, 0, st>>>(partial, stats, blocks_per_frame, groups, cnt, eps, fg);
+    gn_apply_kernel<float, float, false><<<g2, 256, 0, st>>>((const float*)x, (float*)y, stats, w, b, hw, C, groups, total_vec);
   }
   VDA_CUDA_LAUNCH_CHECK("groupnorm kernels");
   return 0;

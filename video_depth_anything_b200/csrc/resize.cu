@@ -6,8 +6,8 @@ namespace {
 
 // ATen upsample_bilinear2d semantics (align_corners=True): src = dst * (in-1)/(out-1), lambda in fp32,
 // value = h0*(w0*a + w1*b) + h1*(w0*c + w1*d), computed in fp32 and rounded once to the storage type.
-template <typename T>
-__global__ void __launch_bounds__(256) bilinear_kernel(const T* __restrict__ in, T* __restrict__ out, int ih, int iw,
+template <typename T, typename TO>
+__global__ void __launch_bounds__(256) bilinear_kernel(const T* __restrict__ in, TO* __restrict__ out, int ih, int iw,
                                                       int ipad, int oh, int ow, int opad, int C, float rh, float rw,
                                                       long long total_vec) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(256) bilinear_kernel(const T* __restrict__ in,
 #pragma unroll
   for (int i = 0; i < 8; ++i) o[i] = h0l * (w0l * a[i] + w1l * b[i]) + h1l * (w0l * c[i] + w1l * d[i]);
   const int OW = ow + 2 * opad, OH = oh + 2 * opad;
-  Vec8<T>::store(out + (((long long)f * OH + oy + opad) * OW + ox + opad) * C + cv * 8, o);
+  Vec8<TO>::store(out + (((long long)f * OH + oy + opad) * OW + ox + opad) * C + cv * 8, o);
 }
 
 template <typename T>
@@ -107,8 +107,8 @@ __global__ void pos_bicubic_kernel(const float* __restrict__ pos, float* __restr
 
 }  // namespace
 
-extern "C" int vda_bilinear(const void* in, void* out, int32_t dtype, int32_t frames, int32_t ih, int32_t iw,
-                            int32_t in_padded, int32_t oh, int32_t ow, int32_t out_padded, int32_t C,
+extern "C" int vda_bilinear(const void* in, int32_t in_dtype, void* out, int32_t out_dtype, int32_t frames, int32_t ih,
+                            int32_t iw, int32_t in_padded, int32_t oh, int32_t ow, int32_t out_padded, int32_t C,
                             vda_stream_t stream) {
   VDA_CHECK_ARG(C % 8 == 0, "vda_bilinear: C=%d must be a multiple of 8", C);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -116,12 +116,13 @@ extern "C" int vda_bilinear(const void* in, void* out, int32_t dtype, int32_t fr
   const float rw = ow > 1 ? (float)(iw - 1) / (float)(ow - 1) : 0.f;
   const long long total = (long long)frames * oh * ow * (C / 8);
   const unsigned grid = (unsigned)((total + 255) / 256);
-  if (dtype == VDA_BF16)
-    bilinear_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)in, (bf16*)out, ih, iw, in_padded ? 1 : 0, oh, ow,
-                                                out_padded ? 1 : 0, C, rh, rw, total);
-  else
-    bilinear_kernel<float><<<grid, 256, 0, st>>>((const float*)in, (float*)out, ih, iw, in_padded ? 1 : 0, oh, ow,
-                                                 out_padded ? 1 : 0, C, rh, rw, total);
+  const int ip = in_padded ? 1 : 0, op = out_padded ? 1 : 0;
+#define BL(TI, TO) bilinear_kernel<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, (TO*)out, ih, iw, ip, oh, ow, op, C, rh, rw, total)
+  if (in_dtype == VDA_BF16 && out_dtype == VDA_BF16) BL(bf16, bf16);
+  else if (in_dtype == VDA_BF16 && out_dtype == VDA_F32) BL(bf16, float);
+  else if (in_dtype == VDA_F32 && out_dtype == VDA_F32) BL(float, float);
+  else VDA_CHECK_ARG(false, "vda_bilinear: unsupported dtypes %d -> %d", in_dtype, out_dtype);
+#undef BL
   VDA_CUDA_LAUNCH_CHECK("bilinear_kernel");
   return 0;
 }

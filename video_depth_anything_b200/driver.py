@@ -113,7 +113,7 @@ class WindowedDepthDriver:
         for k in range(len(idx_rows)):
             torch.index_select(pre, 0, sel_all[k], out=plan.x_in)
             plan.launch()
-            L.check(self.lib.vda_resize_depth(plan.depth.data_ptr(), plan.dcode, raw[k * INFER_LEN].data_ptr(), INFER_LEN,
+            L.check(self.lib.vda_resize_depth(plan.depth.data_ptr(), L.F32, raw[k * INFER_LEN].data_ptr(), INFER_LEN,
                                               nh, nw, fh, fw, st), "vda_resize_depth")
         return raw
 

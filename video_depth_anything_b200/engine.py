@@ -105,13 +105,9 @@ class PackedWeights:
                     vec(f"ref{i}.rcu{u}.c{c}.b", sd[f"{r}resConfUnit{u}.conv{c}.bias"])
         mat("oc1.w", _conv3x3_pack(sd[sc + "output_conv1.weight"]))
         vec("oc1.b", sd[sc + "output_conv1.bias"])
-        # the fp32 island (dpt_temporal.py:95-97): weights stay fp32; the tensor-core path splits them into bf16 hi + lo
+        # the fp32 island (dpt_temporal.py:95-97): weights stay fp32 (tcgen05 kind::tf32 in the bf16 build)
         w2 = _conv3x3_pack(sd[sc + "output_conv2.0.weight"]).float()
         w["oc2.w32"] = w2.contiguous()
-        if bf16:
-            hi = w2.to(torch.bfloat16)
-            lo = (w2 - hi.float()).to(torch.bfloat16)
-            w["oc2.whl"] = torch.cat([hi, lo], dim=1).contiguous()
         vec("oc2.b", sd[sc + "output_conv2.0.bias"])
         vec("oc2.hw", sd[sc + "output_conv2.2.weight"].reshape(32))
         self.head_b = float(sd[sc + "output_conv2.2.bias"].reshape(()).item())
@@ -146,7 +142,7 @@ class ForwardPlan:
     """Buffers + launch list for `VideoDepthAnything.forward` on x[frames=B*T, 3, H, W] (video_depth.py:58-65)."""
 
     def __init__(self, pw: PackedWeights, batch: int, T: int, H: int, W: int, device, skip_tmp_block=False, use_tc=None,
-                 keep=()):
+                 keep=(), attn_tc=None):
         assert H % 14 == 0 and W % 14 == 0, f"Input image size {H}x{W} is not a multiple of patch size 14"  # patch_embed.py:73-74
         if T > pw.pe_len:
             raise ValueError(f"video length {T} exceeds the positional-encoding length {pw.pe_len} (num_frames)")
@@ -155,6 +151,7 @@ class ForwardPlan:
         self.adt = torch.bfloat16 if pw.bf16 else torch.float32
         self.dcode = L.BF16 if pw.bf16 else L.F32
         self.use_tc = bool(pw.bf16) if use_tc is None else bool(use_tc)
+        self.attn_tc = self.use_tc if attn_tc is None else bool(attn_tc)
         self.batch, self.T, self.H, self.W = batch, T, H, W
         self.BT = batch * T
         self.ph, self.pw_ = H // 14, W // 14
@@ -277,7 +274,7 @@ class ForwardPlan:
             self.layernorm(resid, y, W_[f"b{i}.norm1.w"], W_[f"b{i}.norm1.b"], 1e-6, M, D)
             self.gemm(y, W_[f"b{i}.qkv.w"], M, 3 * D, D, bias=W_[f"b{i}.qkv.b"], out=qkv)
             self.op(lib.vda_attention, qkv.data_ptr(), att.data_ptr(), self.dcode, BT, ntok, pw.heads, int(self.bf16),
-                    int(self.use_tc))
+                    int(self.attn_tc))
             self.gemm(att, W_[f"b{i}.proj.w"], M, D, D, bias=W_[f"b{i}.proj.b"], resid=resid, gamma=W_[f"b{i}.ls1"])
             self.layernorm(resid, y, W_[f"b{i}.norm2.w"], W_[f"b{i}.norm2.b"], 1e-6, M, D)
             self.gemm(y, W_[f"b{i}.fc1.w"], M, 4 * D, D, bias=W_[f"b{i}.fc1.b"], act=L.ACT_GELU, out=hid)
@@ -304,7 +301,7 @@ class ForwardPlan:
         qkv = self.buf(n + ".qkv", M, 3 * C)
         att = self.buf(n + ".att", M, C)
         ff = self.buf(n + ".ff", M, 4 * C)
-        stats = torch.empty((self.BT * 32 * 2,), dtype=torch.float64, device=self.device)
+        stats = torch.empty((self.BT * 32 * 2 * 33,), dtype=torch.float64, device=self.device)
         self.bufs[n + ".stats"] = stats
         self.op(lib.vda_groupnorm_tokens, x.data_ptr(), self.dcode, g.data_ptr(), self.dcode, W_[n + ".gn.w"].data_ptr(),
                 W_[n + ".gn.b"].data_ptr(), 1e-6, self.BT, hw, C, 32, stats.data_ptr(), launches=3)
@@ -345,7 +342,7 @@ class ForwardPlan:
         r = self.padded(n + ".r", h, w, F)
         self._rcu(n + ".rcu2", s, s_relu, h, w, F, r)
         u = self.buf(n + ".u", self.BT * oh * ow, F)
-        self.op(self._lib.vda_bilinear, r.data_ptr(), u.data_ptr(), self.dcode, self.BT, h, w, 1, oh, ow, 0, F)
+        self.op(self._lib.vda_bilinear, r.data_ptr(), self.dcode, u.data_ptr(), self.dcode, self.BT, h, w, 1, oh, ow, 0, F)
         self.gemm(u, W_[n + ".out.w"], self.BT * oh * ow, F, F, geo=(self.BT, oh, ow), bias=W_[n + ".out.b"], out=out,
                   out_map=out_map)
 
@@ -408,17 +405,16 @@ class ForwardPlan:
         # output_conv1 -> bilinear to (14ph, 14pw) -> fp32 island output_conv2 (dpt_temporal.py:91-99)
         o1 = self.buf("oc1", BT * h0 * w0, F // 2)
         self.conv3x3(p1, "oc1.w", h0, w0, F, F // 2, bias=W_["oc1.b"], out=o1, out_map=L.MAP_DENSE)
-        up = self.padded("up", self.H, self.W, F // 2)
-        self.op(lib.vda_bilinear, o1.data_ptr(), up.data_ptr(), self.dcode, BT, h0, w0, 0, self.H, self.W, 1, F // 2)
-        depth = torch.empty((BT, self.H, self.W), dtype=self.adt, device=self.device)
+        # upsample_bilinear2d is an fp32 op under CUDA autocast: `up` is fp32 and un-rounded in both builds, and so is
+        # everything after it (ori_type is fp32, so `out.to(ori_type)` at dpt_temporal.py:99 is a no-op)
+        up = self.buf("up", BT * (self.H + 2) * (self.W + 2), F // 2, torch.float32, zero=True)
+        self.op(lib.vda_bilinear, o1.data_ptr(), self.dcode, up.data_ptr(), L.F32, BT, h0, w0, 0, self.H, self.W, 1, F // 2)
+        depth = torch.empty((BT, self.H, self.W), dtype=torch.float32, device=self.device)
         self.bufs["depth"] = depth
         Mup = BT * (self.H + 2) * (self.W + 2)
-        if self.use_tc:
-            self.gemm(up, W_["oc2.whl"], Mup, 32, F // 2, taps=9, ksplit=2, geo=(BT, self.H, self.W), m_padded=1,
-                      bias=W_["oc2.b"], out_map=L.MAP_DENSE, head_w=W_["oc2.hw"], head_out=depth, head_b=pw.head_b)
-        else:
-            self.gemm(up, W_["oc2.w32"], Mup, 32, F // 2, taps=9, geo=(BT, self.H, self.W), m_padded=1, bias=W_["oc2.b"],
-                      out_map=L.MAP_DENSE, head_w=W_["oc2.hw"], head_out=depth, head_b=pw.head_b)
+        # fp32 operands: SIMT fp32 FMA in the fp32 build, tcgen05 kind::tf32 in the bf16 build (cuDNN's default for fp32 convs)
+        self.gemm(up, W_["oc2.w32"], Mup, 32, F // 2, taps=9, geo=(BT, self.H, self.W), m_padded=1, bias=W_["oc2.b"],
+                  out_map=L.MAP_DENSE, head_w=W_["oc2.hw"], head_out=depth, head_b=pw.head_b)
         self.depth = depth
 
     # ------------------------------------------------------------------ execution

@@ -44,6 +44,7 @@ class VideoDepthAnything(nn.Module):
         self._packed = {}   # (device, bf16) -> (version key, PackedWeights)
         self._plans = {}    # (device, bf16, B, T, H, W, skip) -> ForwardPlan
         self.force_simt = False  # tests: run the bf16 build on the SIMT kernels instead of tcgen05
+        self.attn_simt = False   # tests: tcgen05 GEMMs but the exact-rounding SIMT attention
 
     # ------------------------------------------------------------------ weights / plans
     def _weights_version(self):
@@ -61,10 +62,10 @@ class VideoDepthAnything(nn.Module):
     def plan(self, B, T, H, W, device, bf16, skip_tmp_block=False, keep=()):
         pw = self._packed_weights(device, bf16)
         use_tc = bf16 and not self.force_simt
-        key = (str(device), bf16, B, T, H, W, bool(skip_tmp_block), use_tc, tuple(sorted(keep)))
+        key = (str(device), bf16, B, T, H, W, bool(skip_tmp_block), use_tc, self.attn_simt, tuple(sorted(keep)))
         p = self._plans.get(key)
         if p is None:
-            p = ForwardPlan(pw, B, T, H, W, device, skip_tmp_block, use_tc=use_tc, keep=keep)
+            p = ForwardPlan(pw, B, T, H, W, device, skip_tmp_block, use_tc=use_tc, keep=keep, attn_tc=use_tc and not self.attn_simt)
             self._plans[key] = p
         return p
 
@@ -73,11 +74,11 @@ class VideoDepthAnything(nn.Module):
         B, T, Cc, H, W = x.shape
         L.require_device(x.device)
         bf16 = torch.is_autocast_enabled("cuda") if hasattr(torch, "is_autocast_enabled") else False
-        out_dtype = torch.get_autocast_dtype("cuda") if bf16 else torch.float32
         plan = self.plan(B, T, H, W, x.device, bf16, skip_tmp_block)
         depth = plan.run(x.to(torch.float32).flatten(0, 1))
-        # the reference returns a fresh tensor in the autocast dtype; the identity resize + ReLU are no-ops (:63-64)
-        return depth.to(out_dtype, copy=True).unflatten(0, (B, T))
+        # fp32 in both builds: under CUDA autocast the head's bilinear upsample is an fp32 op, so the output convs and
+        # the result stay fp32; the identity resize + ReLU of video_depth.py:63-64 are numerical no-ops.
+        return depth.clone().unflatten(0, (B, T))
 
     # ------------------------------------------------------------------ driver (video_depth.py:329-417)
     def infer_video_depth(self, frames, target_fps, input_size=518, device="cuda", fp32=False, skip_tmp_block=False):
