@@ -1,0 +1,163 @@
+// Coalesced epilogue of the tcgen05 GEMM (bf16 build).  One call handles a chunk of 64 OUTPUT columns for the 32 rows
+// (TMEM lanes) owned by one epilogue warp:
+//   phase 1 (thread == row): tcgen05.ld the accumulators, add the bias (smem tile, broadcast reads), apply the
+//            activation, round to bf16 (every value is a bf16 number at this point under autocast, so staging in
+//            bf16 is lossless) and park the 64 values in a 128B-swizzled per-warp smem tile;
+//   phase 2 (8 lanes == one row segment of 64 columns, 4 rows per instruction): read the tile back transposed and do
+//            all global traffic -- residual stream read-modify-write, skip-connection reads, output stores -- as
+//            16/32-byte per-lane accesses that cover whole 128-byte lines.
+// The semantic twin is epi_chunk() in epilogue.cuh (used by the SIMT build and as the fallback for ragged chunks);
+// any change to rounding points must be made in both.
+#pragma once
+#include "epilogue.cuh"
+#include "ptx.cuh"
+
+struct RowIdx {
+  int out_row, res_row, resid_row;  // -1 = this row produces no output
+};
+
+__device__ __forceinline__ RowIdx make_row_idx(const Epi& e, int m) {
+  RowCtx r = make_row_ctx(e, m);
+  RowIdx x;
+  x.res_row = (int)r.res_row;
+  x.resid_row = (int)r.resid_row;
+  if (e.out_map == VDA_MAP_CONVT)  // padded row of (b, y*k, x*k); the (ky, kx) of the column block is added per chunk
+    x.out_row = (int)(((long long)r.b * (e.gh * e.ct_k + 2) + r.y * e.ct_k + 1) * (e.gw * e.ct_k + 2) + r.x * e.ct_k + 1);
+  else
+    x.out_row = (int)r.out_row;
+  if (!r.valid) x.out_row = -1;
+  return x;
+}
+
+// Is the chunk of 64 output columns starting at accumulator column n (global) eligible for the coalesced path?
+__device__ __forceinline__ bool epi_fast_ok(const Epi& e, int n) {
+  const bool geglu = e.act == VDA_ACT_GEGLU;
+  const int ncols = geglu ? (e.N >> 1) : e.N;
+  const int c0 = geglu ? (n >> 1) : n;
+  if (e.head_w != nullptr || c0 + 64 > ncols) return false;
+  if ((e.ldo & 7) || (e.ldres & 7) || (e.ldresid & 3)) return false;
+  if (e.out_map == VDA_MAP_CONVT && (e.ct_cout & 63)) return false;
+  return true;
+}
+
+// stage: this warp's 4 KB tile (1024B aligned); sbias: bias values of the CTA tile's accumulator columns, indexed by
+// the tile-local accumulator column; tcol: TMEM address of (this warp's lane quadrant, tile-local accumulator column c).
+template <bool GEGLU>
+__device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int n0, int c, uint32_t tcol, uint8_t* stage,
+                                             const float* sbias, int lane) {
+  uint32_t pk[32];
+  // ---------------------------------------------------------------- phase 1
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    float v[32];
+    if constexpr (GEGLU) {
+      float g[32];
+      ptx::tmem_ld32(tcol + h * 64, v);
+      ptx::tmem_ld32(tcol + h * 64 + 32, g);
+      ptx::tmem_ld_wait();
+      const float* bv = sbias + c + h * 64;
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        const float4 b4 = *reinterpret_cast<const float4*>(bv + i), g4 = *reinterpret_cast<const float4*>(bv + 32 + i);
+        const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, gb[4] = {g4.x, g4.y, g4.z, g4.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float val = round_bf16(v[i + k] + bb[k]), gate = round_bf16(g[i + k] + gb[k]);
+          v[i + k] = val * round_bf16(gelu_erf(gate));
+        }
+      }
+    } else {
+      ptx::tmem_ld32(tcol + h * 32, v);
+      ptx::tmem_ld_wait();
+      const float* bv = sbias + c + h * 32;
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        const float4 b4 = *reinterpret_cast<const float4*>(bv + i);
+        const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float t = v[i + k] + bb[k];
+          if (e.act == VDA_ACT_GELU) t = gelu_erf(round_bf16(t));
+          else if (e.act == VDA_ACT_RELU) t = fmaxf(t, 0.f);
+          v[i + k] = t;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) pk[h * 16 + (i >> 1)] = pack_bf16x2(v[i], v[i + 1]);
+  }
+  {
+    uint8_t* rowp = stage + lane * 128;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4)) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+  }
+  __syncwarp();
+  // ---------------------------------------------------------------- phase 2
+  const int j = lane & 7;
+  const int col = (GEGLU ? ((n0 + c) >> 1) : (n0 + c)) + 8 * j;  // first of this lane's 8 output columns
+  int ocol = col;
+  int row_add = 0;
+  if (e.out_map == VDA_MAP_CONVT) {
+    const int kk = col / e.ct_cout;
+    ocol = col - kk * e.ct_cout;
+    row_add = (kk / e.ct_k) * (e.gw * e.ct_k + 2) + (kk % e.ct_k);
+  }
+  float gam[8];
+  if (e.resid != nullptr && !e.resid_assign) {
+    const float4 g0 = *reinterpret_cast<const float4*>(e.gamma + col), g1 = *reinterpret_cast<const float4*>(e.gamma + col + 4);
+    gam[0] = g0.x; gam[1] = g0.y; gam[2] = g0.z; gam[3] = g0.w; gam[4] = g1.x; gam[5] = g1.y; gam[6] = g1.z; gam[7] = g1.w;
+  }
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    const int rr = 4 * t + (lane >> 3);
+    const uint4 p = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((j ^ (rr & 7)) << 4));
+    const int orow = __shfl_sync(0xffffffffu, ri.out_row, rr);
+    const int rrow = __shfl_sync(0xffffffffu, ri.res_row, rr);
+    const int drow = __shfl_sync(0xffffffffu, ri.resid_row, rr);
+    if (orow < 0) continue;
+    float v[8] = {bf16lo_to_f32(p.x), bf16hi_to_f32(p.x), bf16lo_to_f32(p.y), bf16hi_to_f32(p.y),
+                  bf16lo_to_f32(p.z), bf16hi_to_f32(p.z), bf16lo_to_f32(p.w), bf16hi_to_f32(p.w)};
+    if (e.resid != nullptr) {
+      float* rp = e.resid + (long long)drow * e.ldresid + col;
+      float4 x0, x1;
+      if (e.resid_assign) {
+        const float* pp = e.pos + (long long)(drow % e.pos_rows) * e.ldresid + col;
+        x0 = *reinterpret_cast<const float4*>(pp);
+        x1 = *reinterpret_cast<const float4*>(pp + 4);
+        x0.x = __fadd_rn(v[0], x0.x); x0.y = __fadd_rn(v[1], x0.y); x0.z = __fadd_rn(v[2], x0.z); x0.w = __fadd_rn(v[3], x0.w);
+        x1.x = __fadd_rn(v[4], x1.x); x1.y = __fadd_rn(v[5], x1.y); x1.z = __fadd_rn(v[6], x1.z); x1.w = __fadd_rn(v[7], x1.w);
+      } else {
+        x0 = *reinterpret_cast<const float4*>(rp);
+        x1 = *reinterpret_cast<const float4*>(rp + 4);
+        x0.x = __fadd_rn(x0.x, __fmul_rn(v[0], gam[0])); x0.y = __fadd_rn(x0.y, __fmul_rn(v[1], gam[1]));
+        x0.z = __fadd_rn(x0.z, __fmul_rn(v[2], gam[2])); x0.w = __fadd_rn(x0.w, __fmul_rn(v[3], gam[3]));
+        x1.x = __fadd_rn(x1.x, __fmul_rn(v[4], gam[4])); x1.y = __fadd_rn(x1.y, __fmul_rn(v[5], gam[5]));
+        x1.z = __fadd_rn(x1.z, __fmul_rn(v[6], gam[6])); x1.w = __fadd_rn(x1.w, __fmul_rn(v[7], gam[7]));
+      }
+      *reinterpret_cast<float4*>(rp) = x0;
+      *reinterpret_cast<float4*>(rp + 4) = x1;
+      if (e.out == nullptr) continue;
+    }
+    if (e.res) {
+      float r8[8];
+      Vec8<bf16>::load(reinterpret_cast<const bf16*>(e.res) + (long long)rrow * e.ldres + ocol, r8);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = round_bf16(v[k] + r8[k]);
+    }
+    if (e.res2) {
+      float r8[8];
+      Vec8<bf16>::load(reinterpret_cast<const bf16*>(e.res2) + (long long)rrow * e.ldres + ocol, r8);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = round_bf16(v[k] + r8[k]);
+    }
+    const long long oo = (long long)(orow + row_add) * e.ldo + ocol;
+    Vec8<bf16>::store(reinterpret_cast<bf16*>(e.out) + oo, v);
+    if (e.out_relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+      Vec8<bf16>::store(reinterpret_cast<bf16*>(e.out_relu) + oo, v);
+    }
+  }
+  __syncwarp();  // the tile is rewritten by the next chunk
+}

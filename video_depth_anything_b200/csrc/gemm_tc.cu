@@ -4,7 +4,7 @@
 // Tile 128 x BN x 64, UMMA 128 x BN x 16 (cta_group::1), STAGES-deep smem ring, two TMEM accumulator stages so the
 // epilogue of tile i overlaps the main loop of tile i+1.  A 3x3 convolution is the same kernel: with padded
 // channels-last activations each tap is a constant row offset of the A tensor map (K loop = 9 taps x K/64).
-#include "epilogue.cuh"
+#include "epilogue_tc.cuh"
 #include "ptx.cuh"
 #include "tmap.h"
 
@@ -13,6 +13,7 @@ namespace {
 constexpr int BM = 128, BK = 64;
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
+constexpr int SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 
 template <int BN>
 struct TcCfg {
@@ -21,7 +22,8 @@ struct TcCfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
   static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;  // power of two for BN in {32,64,128,256}
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int EPI_BYTES = NUM_EPI_WARPS * 4096 /*staging tiles*/ + 2 * BN * 4 /*bias tiles*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 256 /*barriers*/;
 };
 
 struct TcArgs {
@@ -36,9 +38,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcArgs a,
                const Epi e) {
   using C = TcCfg<BN>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* epi_smem = smem + C::STAGES * C::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + C::EPI_BYTES);
   uint64_t* full = bars;                     // [STAGES]   TMA -> MMA
   uint64_t* empty = bars + C::STAGES;        // [STAGES]   MMA -> TMA
   uint64_t* tfull = bars + 2 * C::STAGES;    // [2]        MMA -> epilogue
@@ -52,6 +54,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int num_tiles = a.tiles_m * a.tiles_n;
 
   if (warp == 0 && lane == 0) {
+    if (ptx::smem_u32(smem) & 1023) {
+      printf("vda gemm_tc: dynamic shared memory is not 1024B aligned\n");
+      __trap();
+    }
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
     for (int s = 0; s < C::STAGES; ++s) {
@@ -128,25 +134,47 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps
+    const int ew = warp - 2;                   // 0..7
     const int q = warp & 3;                    // TMEM lane quadrant this warp may access
-    const int half = (warp - 2) >> 2;          // which interleaved set of column chunks
-    const int cw = (e.act == VDA_ACT_GEGLU) ? 64 : 32;
+    const int half = ew >> 2;                  // which interleaved set of column chunks
+    const int et = threadIdx.x - 64;           // 0..255
+    const bool geglu = e.act == VDA_ACT_GEGLU;
+    const int cw = geglu ? 128 : 64;           // accumulator columns per chunk (64 output columns)
+    uint8_t* stage = epi_smem + ew * 4096;
+    float* sbias_all = reinterpret_cast<float*>(epi_smem + NUM_EPI_WARPS * 4096);
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (tile / a.tiles_n) * BM, n0 = (tile % a.tiles_n) * BN;
+      // bias values of this tile's columns -> smem (double-buffered with the accumulator stage: one barrier per tile)
+      float* sbias = sbias_all + acc * BN;
+      for (int i = et; i < BN; i += NUM_EPI_WARPS * 32) {
+        const int n = n0 + i;
+        sbias[i] = (e.bias != nullptr && n < a.N) ? e.bias[e.ct_k ? (n % e.ct_cout) : n] : 0.f;
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
       ptx::mbar_wait(&tfull[acc], acc_phase);
       ptx::tc_fence_after();
       const int m = m0 + q * 32 + lane;
-      const RowCtx r = make_row_ctx(e, m);
+      const RowIdx ri = make_row_idx(e, m);
       const uint32_t trow = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
       for (int c = half * cw; c < BN; c += 2 * cw) {
         if (n0 + c >= a.N) break;
-        float v[32], g[32];
-        ptx::tmem_ld32(trow + c, v);
-        if (cw == 64) ptx::tmem_ld32(trow + c + 32, g);
-        ptx::tmem_ld_wait();
-        epi_chunk<TO, RB>(e, r, n0 + c, v, g);
+        if (c + cw <= BN && epi_fast_ok(e, n0 + c)) {
+          if (geglu) epi_chunk_tc<true>(e, ri, n0, c, trow + c, stage, sbias, lane);
+          else epi_chunk_tc<false>(e, ri, n0, c, trow + c, stage, sbias, lane);
+        } else {
+          // ragged chunk (N tail, narrow conv-transpose blocks, the fused fp32 head): one row per thread
+          const RowCtx r = make_row_ctx(e, m);
+          const int sw = geglu ? 64 : 32;
+          for (int cc = c; cc < c + cw && cc < BN && n0 + cc < a.N; cc += sw) {
+            float v[32], g[32];
+            ptx::tmem_ld32(trow + cc, v);
+            if (geglu) ptx::tmem_ld32(trow + cc + 32, g);
+            ptx::tmem_ld_wait();
+            epi_chunk<TO, RB>(e, r, n0 + cc, v, g);
+          }
+        }
       }
       ptx::tc_fence_before();
       __syncwarp();
@@ -178,6 +206,7 @@ int launch_tc(const vda_gemm_desc* d, cudaStream_t st) {
   const int tiles = a.tiles_m * a.tiles_n;
   const int grid = tiles < vda_sm_count() ? tiles : vda_sm_count();
   Epi e = make_epi(d);
+  static_assert(C::SMEM_BYTES <= SMEM_LIMIT, "shared memory budget exceeded");
   auto kern = gemm_tc_kernel<BN, TO, RB, TF32>;
   static bool attr_set = false;
   if (!attr_set) {
