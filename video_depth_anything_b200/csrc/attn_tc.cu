@@ -1,12 +1,17 @@
 // tcgen05 flash attention for the DINOv2 encoder (dinov2_layers/attention.py:49-59), head_dim 64, non-causal.
 //
-// One CTA = 128 query rows of one (frame, head); two CTAs per SM so one CTA's MMAs overlap the other's softmax.
-//   warp 0   : TMA producer (Q once, then K_j / V_j tiles of 128 keys through 2-stage rings)
-//   warp 1   : MMA issuer;  S = Q K_j^T (128x128x64) and PV = P_j V_j (128x64x128), accumulators in TMEM
-//   warps 2-5: softmax, one query row per thread (TMEM lane == row): S from TMEM, online max/sum in fp32,
-//              P written to shared memory as the bf16 A operand of the PV MMA, O kept in registers.
-// Numerics follow autocast: scores are rounded to bf16 (q@k^T is a bf16 tensor), softmax runs in fp32,
-// probabilities are rounded to bf16 before P@V, the output is rounded to bf16.
+// One CTA = up to 256 query rows (two 128-row tiles) of one (frame, head); one CTA per SM.  The two tiles ping-pong:
+// while softmax group 0 works on its S tile the tensor core computes the other tile's S / PV.
+//   warp 0     : TMA producer (Q tiles once, then K_j / V_j tiles of 128 keys through 3-stage rings)
+//   warp 1     : MMA issuer;  S_t = Q_t K_j^T (128x128x64) and PV_t = P_t V_j (128x64x128), accumulators in TMEM
+//   warps 2-5  : softmax group 0 (tile 0), one query row per thread (TMEM lane == row)
+//   warps 6-9  : softmax group 1 (tile 1)
+// A softmax thread reads its S row out of TMEM ONCE, rounding to bf16 and packing as it goes (64 registers), releases
+// the TMEM tile immediately (the next S MMA overlaps the exponentials), then: online max / sum in fp32, P written to
+// shared memory as the bf16 A operand of the PV MMA, O accumulated in TMEM across key blocks (rescaled lazily, only
+// when the running max moves by more than 2^8).
+// Numerics follow autocast: scores are rounded to bf16 (q@k^T is a bf16 tensor; the 2^-3 scale commutes with the
+// rounding), softmax runs in fp32, probabilities are rounded to bf16 before P@V, the output is rounded to bf16.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tmap.h"
@@ -14,24 +19,53 @@
 namespace {
 
 constexpr int BQ = 128, BKV = 128, HD = 64;
+constexpr int NS = 3;                  // K / V ring depth
 constexpr int TILE_BYTES = 128 * 128;  // 128 rows x 64 bf16
-constexpr int OFF_Q = 0, OFF_K = TILE_BYTES, OFF_V = 3 * TILE_BYTES, OFF_P = 5 * TILE_BYTES, OFF_BAR = 7 * TILE_BYTES;
-constexpr int FA_SMEM = OFF_BAR + 128;
-constexpr int FA_THREADS = 192;
-constexpr uint32_t TM_S = 0, TM_O = 128, TM_COLS = 256;
+constexpr int OFF_Q = 0;                         // 2 tiles
+constexpr int OFF_K = 2 * TILE_BYTES;            // NS tiles
+constexpr int OFF_V = OFF_K + NS * TILE_BYTES;   // NS tiles
+constexpr int OFF_P = OFF_V + NS * TILE_BYTES;   // 2 x (2 atoms of 128 rows x 64 keys)
+constexpr int OFF_BAR = OFF_P + 4 * TILE_BYTES;
+constexpr int FA_SMEM = OFF_BAR + 256;
+constexpr int FA_THREADS = 64 + 256;
+constexpr uint32_t TM_S = 0, TM_O = 256, TM_COLS = 512;  // S_t at TM_S + 128 t, O_t at TM_O + 64 t
 
-enum { B_QFULL = 0, B_KFULL = 1, B_KEMPTY = 3, B_VFULL = 5, B_VEMPTY = 7, B_SFULL = 9, B_SFREE = 10, B_PFULL = 11, B_PVDONE = 12 };
+// barrier indices
+constexpr int B_QFULL = 0;               // 1
+constexpr int B_KFULL = 1;               // NS
+constexpr int B_KEMPTY = B_KFULL + NS;   // NS
+constexpr int B_VFULL = B_KEMPTY + NS;   // NS
+constexpr int B_VEMPTY = B_VFULL + NS;   // NS
+constexpr int B_SFULL = B_VEMPTY + NS;   // 2
+constexpr int B_SFREE = B_SFULL + 2;     // 2
+constexpr int B_PFULL = B_SFREE + 2;     // 2
+constexpr int B_PVDONE = B_PFULL + 2;    // 2
+constexpr int NBARS = B_PVDONE + 2;
+static_assert(NBARS * 8 + 8 <= 256, "barrier area");
+static_assert(FA_SMEM <= 232448, "shared memory budget");
 
-__global__ void __launch_bounds__(FA_THREADS, 2)
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+
+__global__ void __launch_bounds__(FA_THREADS, 1)
 flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ o, int ntok, int heads) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + NBARS);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * BQ, h = blockIdx.y, f = blockIdx.z;
+  const int q0 = blockIdx.x * 2 * BQ, h = blockIdx.y, f = blockIdx.z;
   const int D = heads * HD;
   const int nblk = (ntok + BKV - 1) / BKV;
-  const int row0 = f * ntok;  // first row of this frame in the [frames*ntok, 3D] matrix
+  const int ntiles = (q0 + BQ < ntok) ? 2 : 1;  // the last CTA of a frame may own a single tile
+  const int row0 = f * ntok;                    // first row of this frame in the [frames*ntok, 3D] matrix
 
   if (threadIdx.x == 0) {
     if (ptx::smem_u32(smem) & 1023) {
@@ -40,16 +74,18 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
     }
     ptx::prefetch_tmap(&tm);
     ptx::mbar_init(&bars[B_QFULL], 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < NS; ++s) {
       ptx::mbar_init(&bars[B_KFULL + s], 1);
       ptx::mbar_init(&bars[B_KEMPTY + s], 1);
       ptx::mbar_init(&bars[B_VFULL + s], 1);
       ptx::mbar_init(&bars[B_VEMPTY + s], 1);
     }
-    ptx::mbar_init(&bars[B_SFULL], 1);
-    ptx::mbar_init(&bars[B_SFREE], 4);
-    ptx::mbar_init(&bars[B_PFULL], 4);
-    ptx::mbar_init(&bars[B_PVDONE], 1);
+    for (int t = 0; t < 2; ++t) {
+      ptx::mbar_init(&bars[B_SFULL + t], 1);
+      ptx::mbar_init(&bars[B_SFREE + t], 4);
+      ptx::mbar_init(&bars[B_PFULL + t], 4);
+      ptx::mbar_init(&bars[B_PVDONE + t], 1);
+    }
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -62,12 +98,14 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
   const uint32_t tmem = *tmem_slot;
 
   if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      ptx::mbar_arrive_expect_tx(&bars[B_QFULL], TILE_BYTES);
-      ptx::tma_load_2d(smem + OFF_Q, &tm, h * HD, row0 + q0, &bars[B_QFULL]);
+      ptx::mbar_arrive_expect_tx(&bars[B_QFULL], ntiles * TILE_BYTES);
+      for (int t = 0; t < ntiles; ++t)
+        ptx::tma_load_2d(smem + OFF_Q + t * TILE_BYTES, &tm, h * HD, row0 + q0 + t * BQ, &bars[B_QFULL]);
       for (int j = 0; j < nblk; ++j) {
-        const int s = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
+        const int s = j % NS;
+        const uint32_t ph = (j / NS) & 1;
         ptx::mbar_wait(&bars[B_KEMPTY + s], ph ^ 1);
         ptx::mbar_arrive_expect_tx(&bars[B_KFULL + s], TILE_BYTES);
         ptx::tma_load_2d(smem + OFF_K + s * TILE_BYTES, &tm, D + h * HD, row0 + j * BKV, &bars[B_KFULL + s]);
@@ -77,140 +115,160 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
       }
     }
   } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       constexpr uint32_t idesc_s = ptx::make_idesc_bf16(BQ, BKV, 0, 0);
       constexpr uint32_t idesc_pv = ptx::make_idesc_bf16(BQ, HD, 0, 1);  // B = V is MN-major (d contiguous)
-      const uint32_t sq = ptx::smem_u32(smem + OFF_Q), sp = ptx::smem_u32(smem + OFF_P);
-      const uint64_t dq = ptx::make_sw128_desc(sq, 16, 1024);
-      auto issue_s = [&](int j) {
-        const int s = j & 1;
-        ptx::mbar_wait(&bars[B_KFULL + s], (j >> 1) & 1);
-        ptx::tc_fence_after();
+      auto issue_s = [&](int j) {  // S_t(j) for every tile; frees the K stage when done
+        const int s = j % NS;
+        ptx::mbar_wait(&bars[B_KFULL + s], (j / NS) & 1);
         const uint64_t dk = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_K + s * TILE_BYTES), 16, 1024);
+        for (int t = 0; t < ntiles; ++t) {
+          if (j > 0) ptx::mbar_wait(&bars[B_SFREE + t], (j - 1) & 1);  // softmax t holds S_t(j-1) in registers
+          ptx::tc_fence_after();
+          const uint64_t dq = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_Q + t * TILE_BYTES), 16, 1024);
 #pragma unroll
-        for (int k = 0; k < HD / 16; ++k) ptx::mma_f16_ss(tmem + TM_S, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+          for (int k = 0; k < HD / 16; ++k)
+            ptx::mma_f16_ss(tmem + TM_S + t * BKV, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+          ptx::tc_commit(&bars[B_SFULL + t]);
+        }
         ptx::tc_commit(&bars[B_KEMPTY + s]);
-        ptx::tc_commit(&bars[B_SFULL]);
       };
       ptx::mbar_wait(&bars[B_QFULL], 0);
       issue_s(0);
       for (int j = 0; j < nblk; ++j) {
-        if (j + 1 < nblk) {
-          ptx::mbar_wait(&bars[B_SFREE], j & 1);  // softmax has read S_j out of TMEM
-          issue_s(j + 1);
-        }
-        const int s = j & 1;
-        ptx::mbar_wait(&bars[B_VFULL + s], (j >> 1) & 1);
-        ptx::mbar_wait(&bars[B_PFULL], j & 1);  // P_j is in smem, PV_{j-1} has been read out of TMEM
-        ptx::tc_fence_after();
+        if (j + 1 < nblk) issue_s(j + 1);
+        const int s = j % NS;
+        ptx::mbar_wait(&bars[B_VFULL + s], (j / NS) & 1);
         const uint32_t sv = ptx::smem_u32(smem + OFF_V + s * TILE_BYTES);
+        for (int t = 0; t < ntiles; ++t) {
+          ptx::mbar_wait(&bars[B_PFULL + t], j & 1);  // P_t(j) is in smem, PV_t(j-1) has been read out of TMEM
+          ptx::tc_fence_after();
+          const uint32_t sp = ptx::smem_u32(smem + OFF_P + t * 2 * TILE_BYTES);
 #pragma unroll
-        for (int k = 0; k < BKV / 16; ++k) {
-          const uint64_t dp = ptx::make_sw128_desc(sp + (k >> 2) * TILE_BYTES, 16, 1024) + 2 * (k & 3);
-          const uint64_t dv = ptx::make_sw128_desc(sv + k * 2048, 1024, 1024);
-          ptx::mma_f16_ss(tmem + TM_O, dp, dv, idesc_pv, k != 0);
+          for (int k = 0; k < BKV / 16; ++k) {
+            const uint64_t dp = ptx::make_sw128_desc(sp + (k >> 2) * TILE_BYTES, 16, 1024) + 2 * (k & 3);
+            const uint64_t dv = ptx::make_sw128_desc(sv + k * 2048, 1024, 1024);
+            ptx::mma_f16_ss(tmem + TM_O + t * HD, dp, dv, idesc_pv, (j | k) != 0);  // O accumulates in TMEM
+          }
+          ptx::tc_commit(&bars[B_PVDONE + t]);
         }
         ptx::tc_commit(&bars[B_VEMPTY + s]);
-        ptx::tc_commit(&bars[B_PVDONE]);
       }
     }
   } else {
-    const int q = warp & 3;
-    const int r = q * 32 + lane;  // query row inside the tile == TMEM lane
-    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-    const float LOG2E = 1.4426950408889634f;
-    float oacc[HD];
-#pragma unroll
-    for (int c = 0; c < HD; ++c) oacc[c] = 0.f;
-    float m = -INFINITY, l = 0.f, alpha_prev = 0.f;
-    uint8_t* prow = smem + OFF_P + r * 128;
-    for (int j = 0; j < nblk; ++j) {
-      ptx::mbar_wait(&bars[B_SFULL], j & 1);
-      ptx::tc_fence_after();
-      const int kvalid = ntok - j * BKV;  // keys >= kvalid are outside the frame
-      // pass 1: block max of the bf16-rounded scaled scores
-      float bm = -INFINITY;
-#pragma unroll
-      for (int c0 = 0; c0 < BKV; c0 += 32) {
-        float sv[32];
-        ptx::tmem_ld32(trow + TM_S + c0, sv);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = round_bf16(sv[i] * 0.125f);
-          if (c0 + i < kvalid) bm = fmaxf(bm, s);
-        }
-      }
-      const float m_new = fmaxf(m, bm);
-      const float alpha = exp2f((m - m_new) * LOG2E);
-      const float mb = m_new * LOG2E;
-      // fold PV_{j-1} (relative to the previous max) into the register accumulator before P / O_part are overwritten
-      if (j > 0) {
-        ptx::mbar_wait(&bars[B_PVDONE], (j - 1) & 1);
+    // ------------------------------------------------------------------ softmax groups
+    const int t = (warp - 2) >> 2;  // tile / group
+    if (t < ntiles) {
+      const int q = warp & 3;       // TMEM lane quadrant of this warp
+      const int r = q * 32 + lane;  // query row inside the tile == TMEM lane
+      const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+      const uint32_t ts = trow + TM_S + t * BKV, to = trow + TM_O + t * HD;
+      const float C2 = 0.125f * 1.4426950408889634f;  // scale * log2(e)
+      float m = -INFINITY, l = 0.f;  // m: reference max (RAW, unscaled bf16 scores) of the exponentials; may be stale
+      uint8_t* pbase = smem + OFF_P + t * 2 * TILE_BYTES + r * 128;
+      for (int j = 0; j < nblk; ++j) {
+        ptx::mbar_wait(&bars[B_SFULL + t], j & 1);
         ptx::tc_fence_after();
+        // ---- S row -> registers, rounded to bf16 and packed
+        uint32_t sp[64];
 #pragma unroll
-        for (int c0 = 0; c0 < HD; c0 += 32) {
-          float pv[32];
-          ptx::tmem_ld32(trow + TM_O + c0, pv);
+        for (int c0 = 0; c0 < BKV; c0 += 32) {
+          float sv[32];
+          ptx::tmem_ld32(ts + c0, sv);
           ptx::tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) oacc[c0 + i] = fmaf(oacc[c0 + i], alpha_prev, pv[i]);
+          for (int i = 0; i < 32; i += 2) sp[(c0 + i) >> 1] = pack_bf16x2(sv[i], sv[i + 1]);
         }
-      }
-      // pass 2: probabilities -> bf16 -> swizzled smem (A operand of the PV MMA)
-      float psum = 0.f;
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bars[B_SFREE + t]);  // the next S MMA of this tile may start
+        const int kvalid = ntok - j * BKV;  // keys >= kvalid are outside the frame
+        if (kvalid < BKV) {
 #pragma unroll
-      for (int c0 = 0; c0 < BKV; c0 += 32) {
-        float sv[32];
-        ptx::tmem_ld32(trow + TM_S + c0, sv);
-        ptx::tmem_ld_wait();
-        uint32_t pk[16];
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float s0 = round_bf16(sv[i] * 0.125f), s1 = round_bf16(sv[i + 1] * 0.125f);
-          float p0 = (c0 + i < kvalid) ? exp2f(fmaf(s0, LOG2E, -mb)) : 0.f;
-          float p1 = (c0 + i + 1 < kvalid) ? exp2f(fmaf(s1, LOG2E, -mb)) : 0.f;
-          psum += p0 + p1;
-          pk[i >> 1] = pack_bf16x2(p0, p1);
+          for (int i = 0; i < 64; ++i) {
+            if (2 * i >= kvalid) sp[i] = 0xFF80FF80u;
+            else if (2 * i + 1 >= kvalid) sp[i] = (sp[i] & 0xFFFFu) | 0xFF800000u;
+          }
         }
-        uint8_t* half = prow + (c0 >> 6) * TILE_BYTES;
+        uint32_t mx2 = 0xFF80FF80u;  // (-inf, -inf)
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int chunk = ((c0 & 63) >> 3) + g;
-          *reinterpret_cast<uint4*>(half + ((chunk ^ (r & 7)) << 4)) =
-              make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+        for (int i = 0; i < 64; ++i) mx2 = bf16x2_max(mx2, sp[i]);
+        const float bm = fmaxf(bf16lo_to_f32(mx2), bf16hi_to_f32(mx2));
+        // Lazy rescale: the reference max only moves when the block max exceeds it by more than 2^8 in the exponent
+        // (probabilities then stay <= 256, harmless in bf16 / fp32); O and l are rescaled only on those blocks.
+        const bool need = (bm - m) * C2 > 8.0f;  // always true on the first block (m = -inf)
+        const float alpha = need ? ex2_approx((m - bm) * C2) : 1.0f;
+        if (need) m = bm;
+        const float mb = m * C2;
+        // ---- probabilities -> bf16 (in place)
+        float psum0 = 0.f, psum1 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+          const float p0 = ex2_approx(fmaf(bf16lo_to_f32(sp[i]), C2, -mb));
+          const float p1 = ex2_approx(fmaf(bf16hi_to_f32(sp[i]), C2, -mb));
+          psum0 += p0;
+          psum1 += p1;
+          sp[i] = pack_bf16x2(p0, p1);
         }
-      }
-      l = fmaf(l, alpha, psum);
-      m = m_new;
-      alpha_prev = alpha;
-      ptx::fence_proxy_async();  // generic-proxy P writes -> visible to the tensor core (async proxy)
-      ptx::tc_fence_before();    // all TMEM reads of S_j and PV_{j-1} are complete
-      __syncwarp();
-      if (lane == 0) {
-        ptx::mbar_arrive(&bars[B_SFREE]);
-        ptx::mbar_arrive(&bars[B_PFULL]);
-      }
-    }
-    ptx::mbar_wait(&bars[B_PVDONE], (nblk - 1) & 1);
-    ptx::tc_fence_after();
+        l = fmaf(l, alpha, psum0 + psum1);
+        // ---- PV_{j-1} must be complete before P (smem) is overwritten or O (TMEM) is rescaled
+        if (j > 0) {
+          ptx::mbar_wait(&bars[B_PVDONE + t], (j - 1) & 1);
+          ptx::tc_fence_after();
+          if (__any_sync(0xffffffffu, need)) {
 #pragma unroll
-    for (int c0 = 0; c0 < HD; c0 += 32) {
-      float pv[32];
-      ptx::tmem_ld32(trow + TM_O + c0, pv);
+            for (int c0 = 0; c0 < HD; c0 += 32) {
+              float ov[32];
+              ptx::tmem_ld32(to + c0, ov);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) ov[i] *= alpha;
+              ptx::tmem_st32(to + c0, ov);
+            }
+            ptx::tmem_st_wait();
+          }
+        }
+        // ---- P -> swizzled smem (A operand of the PV MMA)
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          uint8_t* half = pbase + a * TILE_BYTES;
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            *reinterpret_cast<uint4*>(half + ((g ^ (r & 7)) << 4)) =
+                make_uint4(sp[a * 32 + 4 * g], sp[a * 32 + 4 * g + 1], sp[a * 32 + 4 * g + 2], sp[a * 32 + 4 * g + 3]);
+        }
+        ptx::fence_proxy_async();  // generic-proxy P writes -> visible to the tensor core (async proxy)
+        ptx::tc_fence_before();    // TMEM accesses of this iteration are complete
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bars[B_PFULL + t]);
+      }
+      ptx::mbar_wait(&bars[B_PVDONE + t], (nblk - 1) & 1);
+      ptx::tc_fence_after();
+      float oacc[HD];
+#pragma unroll
+      for (int c0 = 0; c0 < HD; c0 += 32) ptx::tmem_ld32(to + c0, oacc + c0);
       ptx::tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; ++i) oacc[c0 + i] = fmaf(oacc[c0 + i], alpha_prev, pv[i]);
-    }
-    if (q0 + r < ntok) {
+      // ---- normalise, round, and store through this warp's (now idle) P rows so that global stores are row-contiguous
       const float inv = 1.f / l;
-      bf16* op = o + ((long long)row0 + q0 + r) * D + h * HD;
+      uint8_t* wst = smem + OFF_P + t * 2 * TILE_BYTES + q * 32 * 128;  // 32 rows x 128 B, private to this warp
 #pragma unroll
-      for (int c = 0; c < HD; c += 8) {
-        float t[8];
+      for (int g = 0; g < 8; ++g) {
+        uint4 u;
+        u.x = pack_bf16x2(oacc[8 * g] * inv, oacc[8 * g + 1] * inv);
+        u.y = pack_bf16x2(oacc[8 * g + 2] * inv, oacc[8 * g + 3] * inv);
+        u.z = pack_bf16x2(oacc[8 * g + 4] * inv, oacc[8 * g + 5] * inv);
+        u.w = pack_bf16x2(oacc[8 * g + 6] * inv, oacc[8 * g + 7] * inv);
+        *reinterpret_cast<uint4*>(wst + lane * 128 + ((g ^ (lane & 7)) << 4)) = u;
+      }
+      __syncwarp();
+      const int g = lane & 7;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) t[i] = oacc[c + i] * inv;
-        Vec8<bf16>::store(op + c, t);
+      for (int it = 0; it < 8; ++it) {
+        const int rr = 4 * it + (lane >> 3);
+        const int qrow = q0 + t * BQ + q * 32 + rr;
+        const uint4 u = *reinterpret_cast<const uint4*>(wst + rr * 128 + ((g ^ (rr & 7)) << 4));
+        if (qrow < ntok) *reinterpret_cast<uint4*>(o + ((long long)row0 + qrow) * D + h * HD + 8 * g) = u;
       }
     }
     ptx::tc_fence_before();
@@ -238,7 +296,7 @@ int vda_attention_tc(const void* qkv, void* o, int frames, int ntok, int heads, 
     }
     attr_set = true;
   }
-  dim3 grid((ntok + BQ - 1) / BQ, heads, frames);
+  dim3 grid((ntok + 2 * BQ - 1) / (2 * BQ), heads, frames);
   flash_attn_tc_kernel<<<grid, FA_THREADS, FA_SMEM, st>>>(tm, reinterpret_cast<bf16*>(o), ntok, heads);
   VDA_CUDA_LAUNCH_CHECK("flash_attn_tc_kernel");
   return 0;
