@@ -63,7 +63,7 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const float val = round_bf16(v[i + k] + bb[k]), gate = round_bf16(g[i + k] + gb[k]);
-          v[i + k] = val * round_bf16(gelu_erf(gate));
+          v[i + k] = val * round_bf16(gelu_fast(gate));
         }
       }
     } else {
@@ -77,7 +77,7 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           float t = v[i + k] + bb[k];
-          if (e.act == VDA_ACT_GELU) t = gelu_erf(round_bf16(t));
+          if (e.act == VDA_ACT_GELU) t = gelu_fast(round_bf16(t));
           else if (e.act == VDA_ACT_RELU) t = fmaxf(t, 0.f);
           v[i + k] = t;
         }
@@ -128,15 +128,18 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
         x0.x = __fadd_rn(v[0], x0.x); x0.y = __fadd_rn(v[1], x0.y); x0.z = __fadd_rn(v[2], x0.z); x0.w = __fadd_rn(v[3], x0.w);
         x1.x = __fadd_rn(v[4], x1.x); x1.y = __fadd_rn(v[5], x1.y); x1.z = __fadd_rn(v[6], x1.z); x1.w = __fadd_rn(v[7], x1.w);
       } else {
-        x0 = *reinterpret_cast<const float4*>(rp);
-        x1 = *reinterpret_cast<const float4*>(rp + 4);
-        x0.x = __fadd_rn(x0.x, __fmul_rn(v[0], gam[0])); x0.y = __fadd_rn(x0.y, __fmul_rn(v[1], gam[1]));
-        x0.z = __fadd_rn(x0.z, __fmul_rn(v[2], gam[2])); x0.w = __fadd_rn(x0.w, __fmul_rn(v[3], gam[3]));
-        x1.x = __fadd_rn(x1.x, __fmul_rn(v[4], gam[4])); x1.y = __fadd_rn(x1.y, __fmul_rn(v[5], gam[5]));
-        x1.z = __fadd_rn(x1.z, __fmul_rn(v[6], gam[6])); x1.w = __fadd_rn(x1.w, __fmul_rn(v[7], gam[7]));
+        // resid += gamma * v as a fire-and-forget vector reduction: the L2 performs the single fp32 add (round to
+        // nearest, one adder per element: the same bits as load-add-store, denormals aside: REDG flushes them) and the warp never waits
+        // for the old value to travel to the SM.
+        x0.x = __fmul_rn(v[0], gam[0]); x0.y = __fmul_rn(v[1], gam[1]); x0.z = __fmul_rn(v[2], gam[2]); x0.w = __fmul_rn(v[3], gam[3]);
+        x1.x = __fmul_rn(v[4], gam[4]); x1.y = __fmul_rn(v[5], gam[5]); x1.z = __fmul_rn(v[6], gam[6]); x1.w = __fmul_rn(v[7], gam[7]);
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(rp), "f"(x0.x), "f"(x0.y), "f"(x0.z), "f"(x0.w) : "memory");
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(rp + 4), "f"(x1.x), "f"(x1.y), "f"(x1.z), "f"(x1.w) : "memory");
       }
-      *reinterpret_cast<float4*>(rp) = x0;
-      *reinterpret_cast<float4*>(rp + 4) = x1;
+      if (e.resid_assign) {
+        *reinterpret_cast<float4*>(rp) = x0;
+        *reinterpret_cast<float4*>(rp + 4) = x1;
+      }
       if (e.out == nullptr) continue;
     }
     if (e.res) {

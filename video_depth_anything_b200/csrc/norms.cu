@@ -5,11 +5,39 @@
 namespace {
 
 // ---------------------------------------------------------------- LayerNorm
+// Lane `l` owns the column groups [ (l + 32 j) * V, +V ), V = 16 bytes of input (4 fp32 / 8 bf16), so every warp-wide
+// load, parameter load and store is one contiguous, fully used segment.
+template <typename T, int V> struct VecIO;
+template <> struct VecIO<float, 4> {
+  static __device__ __forceinline__ void load(const float* p, float* v) {
+    const float4 a = *reinterpret_cast<const float4*>(p);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  }
+  static __device__ __forceinline__ void store(float* p, const float* v) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+template <> struct VecIO<float, 8> {
+  static __device__ __forceinline__ void load(const float* p, float* v) { Vec8<float>::load(p, v); }
+  static __device__ __forceinline__ void store(float* p, const float* v) { Vec8<float>::store(p, v); }
+};
+template <> struct VecIO<bf16, 8> {
+  static __device__ __forceinline__ void load(const bf16* p, float* v) { Vec8<bf16>::load(p, v); }
+  static __device__ __forceinline__ void store(bf16* p, const float* v) { Vec8<bf16>::store(p, v); }
+};
+template <> struct VecIO<bf16, 4> {
+  static __device__ __forceinline__ void store(bf16* p, const float* v) {
+    *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
+  }
+};
+
 template <typename TI, typename TO, bool RB>
 __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x, TO* __restrict__ y,
                                                        const float* __restrict__ w, const float* __restrict__ b, float eps,
                                                        long long rows, int D, int group_rows, int skip_first,
                                                        const float* __restrict__ pe, int pe_group, int pe_T) {
+  constexpr int V = 16 / (int)sizeof(TI);    // elements per 16-byte input vector
+  constexpr int MAXV = 1024 / (32 * V);      // vectors per lane for D <= 1024
   const int lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -20,29 +48,28 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x
     if (i == 0) return;
     orow = g * (group_rows - 1) + i - 1;
   }
-  constexpr int MAXV = 4;  // up to 4 x 8 x 32 = 1024 channels
-  const int nv = D >> 3;   // 8-element vectors per row
-  float v[MAXV][8];
+  const int nv = D / V;
+  float v[MAXV][V];
   const TI* xr = x + row * D;
   float s = 0.f;
 #pragma unroll
   for (int j = 0; j < MAXV; ++j) {
-    int c = lane + 32 * j;
+    const int c = lane + 32 * j;
     if (c < nv) {
-      Vec8<TI>::load(xr + c * 8, v[j]);
+      VecIO<TI, V>::load(xr + c * V, v[j]);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) s += v[j][i];
+      for (int i = 0; i < V; ++i) s += v[j][i];
     }
   }
   const float mean = warp_sum(s) / (float)D;
   float ss = 0.f;
 #pragma unroll
   for (int j = 0; j < MAXV; ++j) {
-    int c = lane + 32 * j;
+    const int c = lane + 32 * j;
     if (c < nv) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        float d = v[j][i] - mean;
+      for (int i = 0; i < V; ++i) {
+        const float d = v[j][i] - mean;
         ss = fmaf(d, d, ss);
       }
     }
@@ -52,17 +79,19 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x
   TO* yr = y + orow * D;
 #pragma unroll
   for (int j = 0; j < MAXV; ++j) {
-    int c = lane + 32 * j;
+    const int c = lane + 32 * j;
     if (c < nv) {
-      float o[8];
+      float wv[V], bv[V], pv[V], o[V];
+      VecIO<float, V>::load(w + c * V, wv);
+      VecIO<float, V>::load(b + c * V, bv);
+      if (per) VecIO<float, V>::load(per + c * V, pv);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        int ch = c * 8 + i;
-        float t = w[ch] * (rstd * (v[j][i] - mean)) + b[ch];
-        if (per) t = t + per[ch];
+      for (int i = 0; i < V; ++i) {
+        float t = wv[i] * (rstd * (v[j][i] - mean)) + bv[i];
+        if (per) t = t + pv[i];
         o[i] = R<RB>(t);
       }
-      Vec8<TO>::store(yr + c * 8, o);
+      VecIO<TO, V>::store(yr + c * V, o);
     }
   }
 }
