@@ -12,6 +12,27 @@
 #include "epilogue.cuh"
 #include "ptx.cuh"
 
+// Epilogue kinds: the common shapes are compiled as separate kernels so that their inner loops carry no run-time
+// dispatch (the fully generic body is ~20k SASS instructions and thrashes the instruction cache).
+enum EpiKind {
+  EK_STORE = 0,    // out = R(acc + bias)                                  (qkv, 1x1 projections, plain convs)
+  EK_GELU = 1,     // out = R(gelu(R(acc + bias)))                         (mlp.fc1)
+  EK_RESID = 2,    // resid += gamma * R(acc + bias), nothing else stored  (attn.proj, mlp.fc2)
+  EK_GEGLU = 3,    // out = R(value * R(gelu(gate)))                       (motion-module feed-forward)
+  EK_GENERIC = 4   // everything, decided at run time
+};
+
+static inline int epi_kind_of(const vda_gemm_desc* d) {
+  const bool plain = d->res == nullptr && d->res2 == nullptr && d->out_relu == nullptr && d->head_w == nullptr;
+  if (plain && d->resid == nullptr && d->out != nullptr) {
+    if (d->act == VDA_ACT_NONE) return EK_STORE;
+    if (d->act == VDA_ACT_GELU) return EK_GELU;
+    if (d->act == VDA_ACT_GEGLU) return EK_GEGLU;
+  }
+  if (plain && d->resid != nullptr && !d->resid_assign && d->out == nullptr && d->act == VDA_ACT_NONE) return EK_RESID;
+  return EK_GENERIC;
+}
+
 struct RowIdx {
   int out_row, res_row, resid_row;  // -1 = this row produces no output
 };
@@ -42,9 +63,16 @@ __device__ __forceinline__ bool epi_fast_ok(const Epi& e, int n) {
 
 // stage: this warp's 4 KB tile (1024B aligned); sbias: bias values of the CTA tile's accumulator columns, indexed by
 // the tile-local accumulator column; tcol: TMEM address of (this warp's lane quadrant, tile-local accumulator column c).
-template <bool GEGLU>
+template <int EK, bool GEGLU>
 __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int n0, int c, uint32_t tcol, uint8_t* stage,
                                              const float* sbias, int lane) {
+  static_assert((EK == EK_GEGLU) == GEGLU || EK == EK_GENERIC, "GEGLU flag must match the kind");
+  constexpr bool GEN = EK == EK_GENERIC;
+  const int act = GEN ? e.act : (EK == EK_GELU ? (int)VDA_ACT_GELU : (int)VDA_ACT_NONE);
+  const bool has_resid = GEN ? (e.resid != nullptr) : (EK == EK_RESID);
+  const bool has_out = GEN ? (e.out != nullptr) : (EK != EK_RESID);
+  const bool has_res = GEN && e.res != nullptr, has_res2 = GEN && e.res2 != nullptr, has_relu = GEN && e.out_relu != nullptr;
+  const bool assign = GEN && e.resid_assign;
   uint32_t pk[32];
   // ---------------------------------------------------------------- phase 1
 #pragma unroll
@@ -77,8 +105,8 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           float t = v[i + k] + bb[k];
-          if (e.act == VDA_ACT_GELU) t = gelu_fast(round_bf16(t));
-          else if (e.act == VDA_ACT_RELU) t = fmaxf(t, 0.f);
+          if (act == VDA_ACT_GELU) t = gelu_fast(round_bf16(t));
+          else if (act == VDA_ACT_RELU) t = fmaxf(t, 0.f);
           v[i + k] = t;
         }
       }
@@ -104,7 +132,7 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
     row_add = (kk / e.ct_k) * (e.gw * e.ct_k + 2) + (kk % e.ct_k);
   }
   float gam[8];
-  if (e.resid != nullptr && !e.resid_assign) {
+  if (has_resid && !assign) {
     const float4 g0 = *reinterpret_cast<const float4*>(e.gamma + col), g1 = *reinterpret_cast<const float4*>(e.gamma + col + 4);
     gam[0] = g0.x; gam[1] = g0.y; gam[2] = g0.z; gam[3] = g0.w; gam[4] = g1.x; gam[5] = g1.y; gam[6] = g1.z; gam[7] = g1.w;
   }
@@ -118,10 +146,10 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
     if (orow < 0) continue;
     float v[8] = {bf16lo_to_f32(p.x), bf16hi_to_f32(p.x), bf16lo_to_f32(p.y), bf16hi_to_f32(p.y),
                   bf16lo_to_f32(p.z), bf16hi_to_f32(p.z), bf16lo_to_f32(p.w), bf16hi_to_f32(p.w)};
-    if (e.resid != nullptr) {
+    if (has_resid) {
       float* rp = e.resid + (long long)drow * e.ldresid + col;
       float4 x0, x1;
-      if (e.resid_assign) {
+      if (assign) {
         const float* pp = e.pos + (long long)(drow % e.pos_rows) * e.ldresid + col;
         x0 = *reinterpret_cast<const float4*>(pp);
         x1 = *reinterpret_cast<const float4*>(pp + 4);
@@ -136,19 +164,19 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
         asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(rp), "f"(x0.x), "f"(x0.y), "f"(x0.z), "f"(x0.w) : "memory");
         asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(rp + 4), "f"(x1.x), "f"(x1.y), "f"(x1.z), "f"(x1.w) : "memory");
       }
-      if (e.resid_assign) {
+      if (assign) {
         *reinterpret_cast<float4*>(rp) = x0;
         *reinterpret_cast<float4*>(rp + 4) = x1;
       }
-      if (e.out == nullptr) continue;
+      if (!has_out) continue;
     }
-    if (e.res) {
+    if (has_res) {
       float r8[8];
       Vec8<bf16>::load(reinterpret_cast<const bf16*>(e.res) + (long long)rrow * e.ldres + ocol, r8);
 #pragma unroll
       for (int k = 0; k < 8; ++k) v[k] = round_bf16(v[k] + r8[k]);
     }
-    if (e.res2) {
+    if (has_res2) {
       float r8[8];
       Vec8<bf16>::load(reinterpret_cast<const bf16*>(e.res2) + (long long)rrow * e.ldres + ocol, r8);
 #pragma unroll
@@ -156,7 +184,7 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
     }
     const long long oo = (long long)(orow + row_add) * e.ldo + ocol;
     Vec8<bf16>::store(reinterpret_cast<bf16*>(e.out) + oo, v);
-    if (e.out_relu) {
+    if (has_relu) {
 #pragma unroll
       for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
       Vec8<bf16>::store(reinterpret_cast<bf16*>(e.out_relu) + oo, v);

@@ -33,7 +33,7 @@ struct TcArgs {
   int tiles_m, tiles_n;
 };
 
-template <int BN, typename TO, bool RB, bool TF32>
+template <int BN, typename TO, bool RB, bool TF32, int EK>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcArgs a,
                const Epi e) {
@@ -138,7 +138,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int q = warp & 3;                    // TMEM lane quadrant this warp may access
     const int half = ew >> 2;                  // which interleaved set of column chunks
     const int et = threadIdx.x - 64;           // 0..255
-    const bool geglu = e.act == VDA_ACT_GEGLU;
+    const bool geglu = (EK == EK_GENERIC) ? (e.act == VDA_ACT_GEGLU) : (EK == EK_GEGLU);
     const int cw = geglu ? 128 : 64;           // accumulator columns per chunk (64 output columns)
     uint8_t* stage = epi_smem + ew * 4096;
     float* sbias_all = reinterpret_cast<float*>(epi_smem + NUM_EPI_WARPS * 4096);
@@ -161,8 +161,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int c = half * cw; c < BN; c += 2 * cw) {
         if (n0 + c >= a.N) break;
         if (c + cw <= BN && epi_fast_ok(e, n0 + c)) {
-          if (geglu) epi_chunk_tc<true>(e, ri, n0, c, trow + c, stage, sbias, lane);
-          else epi_chunk_tc<false>(e, ri, n0, c, trow + c, stage, sbias, lane);
+          if constexpr (EK == EK_GENERIC) {
+            if (geglu) epi_chunk_tc<EK_GENERIC, true>(e, ri, n0, c, trow + c, stage, sbias, lane);
+            else epi_chunk_tc<EK_GENERIC, false>(e, ri, n0, c, trow + c, stage, sbias, lane);
+          } else {
+            epi_chunk_tc<EK, EK == EK_GEGLU>(e, ri, n0, c, trow + c, stage, sbias, lane);
+          }
         } else {
           // ragged chunk (N tail, narrow conv-transpose blocks, the fused fp32 head): one row per thread
           const RowCtx r = make_row_ctx(e, m);
@@ -190,7 +194,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
-template <int BN, typename TO, bool RB, bool TF32>
+template <int BN, typename TO, bool RB, bool TF32, int EK = EK_GENERIC>
 int launch_tc(const vda_gemm_desc* d, cudaStream_t st) {
   using C = TcCfg<BN>;
   constexpr int EB = TF32 ? 4 : 2, BKE = 128 / EB;
@@ -207,7 +211,7 @@ int launch_tc(const vda_gemm_desc* d, cudaStream_t st) {
   const int grid = tiles < vda_sm_count() ? tiles : vda_sm_count();
   Epi e = make_epi(d);
   static_assert(C::SMEM_BYTES <= SMEM_LIMIT, "shared memory budget exceeded");
-  auto kern = gemm_tc_kernel<BN, TO, RB, TF32>;
+  auto kern = gemm_tc_kernel<BN, TO, RB, TF32, EK>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t ce = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
@@ -220,6 +224,17 @@ int launch_tc(const vda_gemm_desc* d, cudaStream_t st) {
   kern<<<grid, NUM_THREADS, C::SMEM_BYTES, st>>>(tmA, tmB, a, e);
   VDA_CUDA_LAUNCH_CHECK("gemm_tc_kernel");
   return 0;
+}
+
+template <int BN>
+int launch_kind(const vda_gemm_desc* d, cudaStream_t st) {
+  switch (epi_kind_of(d)) {
+    case EK_STORE: return launch_tc<BN, bf16, true, false, EK_STORE>(d, st);
+    case EK_GELU: return launch_tc<BN, bf16, true, false, EK_GELU>(d, st);
+    case EK_RESID: return launch_tc<BN, bf16, true, false, EK_RESID>(d, st);
+    case EK_GEGLU: return launch_tc<BN, bf16, true, false, EK_GEGLU>(d, st);
+    default: return launch_tc<BN, bf16, true, false, EK_GENERIC>(d, st);
+  }
 }
 
 }  // namespace
@@ -248,7 +263,7 @@ int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
   switch (bn) {
     case 32: return launch_tc<32, bf16, true, false>(d, st);
     case 64: return launch_tc<64, bf16, true, false>(d, st);
-    case 128: return launch_tc<128, bf16, true, false>(d, st);
-    default: return launch_tc<256, bf16, true, false>(d, st);
+    case 128: return launch_kind<128>(d, st);
+    default: return launch_kind<256>(d, st);
   }
 }
