@@ -101,14 +101,15 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
 #pragma unroll
       for (int i = 0; i < 32; i += 4) {
         const float4 b4 = *reinterpret_cast<const float4*>(bv + i);
-        const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+        v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+      }
+      // the activation switch stays outside the element loops: one compact loop runs, the others are never fetched
+      if (act == VDA_ACT_GELU) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          float t = v[i + k] + bb[k];
-          if (act == VDA_ACT_GELU) t = gelu_fast(round_bf16(t));
-          else if (act == VDA_ACT_RELU) t = fmaxf(t, 0.f);
-          v[i + k] = t;
-        }
+        for (int i = 0; i < 32; ++i) v[i] = gelu_fast(round_bf16(v[i]));
+      } else if (act == VDA_ACT_RELU) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
       }
     }
 #pragma unroll
@@ -136,7 +137,7 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
     const float4 g0 = *reinterpret_cast<const float4*>(e.gamma + col), g1 = *reinterpret_cast<const float4*>(e.gamma + col + 4);
     gam[0] = g0.x; gam[1] = g0.y; gam[2] = g0.z; gam[3] = g0.w; gam[4] = g1.x; gam[5] = g1.y; gam[6] = g1.z; gam[7] = g1.w;
   }
-#pragma unroll
+#pragma unroll(GEN ? 2 : 8)
   for (int t = 0; t < 8; ++t) {
     const int rr = 4 * t + (lane >> 3);
     const uint4 p = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((j ^ (rr & 7)) << 4));
@@ -144,6 +145,10 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
     const int rrow = __shfl_sync(0xffffffffu, ri.res_row, rr);
     const int drow = __shfl_sync(0xffffffffu, ri.resid_row, rr);
     if (orow < 0) continue;
+    if constexpr (EK == EK_STORE || EK == EK_GELU || EK == EK_GEGLU) {  // nothing to add: the staged bf16 is the output
+      *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out) + (long long)(orow + row_add) * e.ldo + ocol) = p;
+      continue;
+    }
     float v[8] = {bf16lo_to_f32(p.x), bf16hi_to_f32(p.x), bf16lo_to_f32(p.y), bf16hi_to_f32(p.y),
                   bf16lo_to_f32(p.z), bf16hi_to_f32(p.z), bf16lo_to_f32(p.w), bf16hi_to_f32(p.w)};
     if (has_resid) {
