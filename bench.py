@@ -35,6 +35,16 @@ CLIP_TFLOP = {("vitl", 518): 44.95, ("vits", 518): 3.881}
 T = 32
 
 
+def measured_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/traffic.json)."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["mean_dram_bytes_per_launch"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -249,7 +259,7 @@ def main():
                          "d2h_bytes_per_step": out_host.numel() * 4},
                     gpu_launches=plan.n_launches * a.steps,
                     roofline={"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05; encoder qkv/proj/fc1/fc2)",
-                              "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                              "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": measured_traffic(),
                               "peak_source": which, "launches_per_step": len(enc_gemm), "tflop_per_step": flops_per_step / 1e12,
                               "share_of_step": gemm_ms / ms_total})
         if world == 1 and not a.no_cpu_baseline:

@@ -175,20 +175,26 @@ class WindowedDepthDriver:
             return depth.cpu().numpy()
 
     def _gather_raw(self, raw, n_win, world, rank, fh, fw):
-        """Raw depth blocks of every rank -> rank 0 (point-to-point over NCCL / NVLink; sizes are index arithmetic)."""
-        dist = torch.distributed
-        shards = shard_windows(n_win, world)
-        if rank == 0:
-            full = torch.empty((n_win * INFER_LEN, fh, fw), dtype=torch.float32, device=self.device)
-            full[:raw.shape[0]].copy_(raw)
-            reqs = []
-            for r in range(1, world):
-                lo, cnt = shards[r]
-                if cnt:
-                    reqs.append(dist.irecv(full[lo * INFER_LEN:(lo + cnt) * INFER_LEN], src=r))
-            for q in reqs:
-                q.wait()
-            return full
-        if raw.shape[0]:
-            dist.send(raw, dst=0)
-        return raw
+        return gather_window_blocks(raw, n_win, world, rank)
+
+
+def gather_window_blocks(raw, n_win, world, rank):
+    """Raw depth blocks of every rank -> rank 0, point-to-point (NCCL over NVLink on GPUs; the same code runs over gloo
+    in the CPU tests).  Block sizes follow from `shard_windows`, so no size exchange is needed.  Returns the full
+    [n_win*32, H, W] stack on rank 0 and the local block elsewhere."""
+    dist = torch.distributed
+    shards = shard_windows(n_win, world)
+    if rank == 0:
+        full = torch.empty((n_win * INFER_LEN,) + tuple(raw.shape[1:]), dtype=raw.dtype, device=raw.device)
+        full[:raw.shape[0]].copy_(raw)
+        reqs = []
+        for r in range(1, world):
+            lo, cnt = shards[r]
+            if cnt:
+                reqs.append(dist.irecv(full[lo * INFER_LEN:(lo + cnt) * INFER_LEN], src=r))
+        for q in reqs:
+            q.wait()
+        return full
+    if raw.shape[0]:
+        dist.send(raw.contiguous(), dst=0)
+    return raw
