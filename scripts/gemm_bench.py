@@ -1,0 +1,50 @@
+#!/usr/bin/env python
+"""Isolated timing of the tcgen05 GEMM on the encoder shapes (CUDA events, L2 flushed between launches by working-set size)."""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from video_depth_anything_b200 import lib as L  # noqa: E402
+
+dev = "cuda"
+L.require_device(dev)
+lib = L.load()
+M = 43840
+shapes = [("qkv", 3072, 1024, "store"), ("proj", 1024, 1024, "resid"), ("fc1", 4096, 1024, "gelu"), ("fc2", 1024, 4096, "resid")]
+if len(sys.argv) > 1:
+    shapes = [s for s in shapes if s[0] in sys.argv[1:]]
+for name, N, K, kind in shapes:
+    A = torch.randn(M, K, device=dev).bfloat16()
+    B = (torch.randn(N, K, device=dev) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device=dev)
+    d = L.GemmDesc()
+    d.A, d.B, d.lda, d.ldb, d.rowsA = A.data_ptr(), B.data_ptr(), K, K, M
+    d.a_dtype = d.b_dtype = L.BF16
+    d.M, d.N, d.K, d.taps, d.ksplit = M, N, K, 1, 1
+    d.bias = bias.data_ptr()
+    d.round_bf16, d.out_dtype, d.use_tc = 1, L.BF16, 1
+    keep = []
+    if kind == "resid":
+        resid = torch.randn(M, N, device=dev)
+        gam = torch.rand(N, device=dev)
+        d.resid, d.gamma, d.ldresid = resid.data_ptr(), gam.data_ptr(), N
+        keep += [resid, gam]
+    else:
+        out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+        d.out, d.ldo = out.data_ptr(), N
+        d.act = L.ACT_GELU if kind == "gelu" else L.ACT_NONE
+        keep.append(out)
+    for _ in range(3):
+        L.gemm(d)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n = 20
+    e0.record()
+    for _ in range(n):
+        L.gemm(d)
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / n
+    print(f"{name:5s} M={M} N={N} K={K} {kind:6s}: {us:8.1f} us  {2.0 * M * N * K / us / 1e6:8.1f} TFLOP/s  (VDA_NO_PAIR={os.environ.get('VDA_NO_PAIR', '0')})")

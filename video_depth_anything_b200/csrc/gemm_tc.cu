@@ -4,6 +4,8 @@
 // Tile 128 x BN x 64, UMMA 128 x BN x 16 (cta_group::1), STAGES-deep smem ring, two TMEM accumulator stages so the
 // epilogue of tile i overlaps the main loop of tile i+1.  A 3x3 convolution is the same kernel: with padded
 // channels-last activations each tap is a constant row offset of the A tensor map (K loop = 9 taps x K/64).
+#include <stdlib.h>
+
 #include "epilogue_tc.cuh"
 #include "ptx.cuh"
 #include "tmap.h"
@@ -239,6 +241,18 @@ int launch_kind(const vda_gemm_desc* d, cudaStream_t st) {
 
 }  // namespace
 
+int vda_gemm_tc_pair(const vda_gemm_desc* d, cudaStream_t st);  // gemm_tc2.cu
+
+// VDA_NO_PAIR=1 keeps every GEMM on the single-CTA kernel (A/B measurements).
+static bool pair_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* s = getenv("VDA_NO_PAIR");
+    v = (s && s[0] == '1') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
   const bool tf32 = d->a_dtype == VDA_F32 && d->b_dtype == VDA_F32;
   VDA_CHECK_ARG(tf32 || (d->a_dtype == VDA_BF16 && d->b_dtype == VDA_BF16), "vda_gemm(tc): operands must be bf16/bf16 or f32/f32 (tf32)");
@@ -260,6 +274,9 @@ int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
   else bn = 256;
   // small problems: prefer more tiles over wide tiles so every SM gets work
   if (bn == 256 && (int64_t)((d->M + 127) / 128) * ((d->N + 255) / 256) < vda_sm_count()) bn = 128;
+  // large contractions: CTA pairs (256 x 256 tile per pair, half the B traffic per SM)
+  if (bn == 256 && pair_enabled() && (int64_t)((d->M + 255) / 256) * ((d->N + 255) / 256) >= vda_sm_count() / 2)
+    return vda_gemm_tc_pair(d, st);
   switch (bn) {
     case 32: return launch_tc<32, bf16, true, false>(d, st);
     case 64: return launch_tc<64, bf16, true, false>(d, st);
