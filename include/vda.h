@@ -144,6 +144,14 @@ int vda_temporal_attention(const void* qkv, void* o, int32_t dtype, int32_t batc
 int vda_bilinear(const void* in, int32_t in_dtype, void* out, int32_t out_dtype, int32_t frames, int32_t ih, int32_t iw,
                  int32_t in_padded, int32_t oh, int32_t ow, int32_t out_padded, int32_t C, vda_stream_t stream);
 
+/* Fused output head of the bf16 build (dpt_temporal.py:92-97, dpt.py:118-124): x[frames, ih, iw, C] bf16 (the output_conv1
+ * result, dense channels-last) -> bilinear align_corners=True to (oh, ow) in fp32 (never materialised) -> 3x3 conv C->32,
+ * fp32 weights w[32, 9*C] (k = (dy*3+dx)*C + ci) on the tensor cores in TF32, + bias -> ReLU -> 1x1 conv 32->1 (head_w,
+ * head_b) -> ReLU -> depth[frames, oh, ow] fp32.  C must be a multiple of 32.  Same arithmetic as
+ * vda_bilinear (fp32 out, padded) followed by vda_gemm (taps = 9, f32 operands, head_w), without the fp32 round trip. */
+int vda_output_head(const void* x, const float* w, const float* bias, const float* head_w, float head_b, float* depth,
+                    int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow, vda_stream_t stream);
+
 /* Patch-embed im2col (patch_embed.py:76): x[frames,3,H,W] f32 -> A[frames*(H/14)*(W/14), kpad] (k = c*196+i*14+j; pad = 0). */
 int vda_im2col_patch(const float* x, void* A, int32_t a_dtype, int32_t frames, int32_t H, int32_t W, int32_t kpad,
                      vda_stream_t stream);

@@ -153,3 +153,36 @@ def test_flash_attention_tc(frames, ntok, heads):
     L.check(lib.vda_attention(qkv.data_ptr(), o2.data_ptr(), L.BF16, frames, ntok, heads, 1, 0, st), "attn_simt")
     d2 = stats(f"flash_tc_vs_simt_{ntok}", o.float(), o2.float())
     assert d2["mean_abs"] <= 2.0 * e_ref["mean_abs"]
+
+
+@pytest.mark.parametrize("Ci,ih,iw,oh,ow,frames", [(32, 16, 24, 28, 42, 2), (128, 32, 48, 56, 84, 3), (64, 9, 7, 21, 13, 1),
+                                                   (128, 40, 40, 70, 70, 2)])
+def test_output_head_fused(Ci, ih, iw, oh, ow, frames):
+    """vda_output_head: bilinear (align_corners) -> 3x3 conv (TF32) -> ReLU -> 1x1 -> ReLU without materialising the
+    upsampled fp32 map; must agree with fp64 torch to TF32 accuracy and with the unfused bilinear + vda_gemm pair."""
+    from video_depth_anything_b200.engine import _conv3x3_pack
+    L, lib = _lib()
+    torch.manual_seed(Ci + oh)
+    x = torch.randn(frames, Ci, ih, iw, device=dev).bfloat16()
+    w = torch.randn(32, Ci, 3, 3, device=dev) / (9 * Ci) ** 0.5
+    b, hw_, hb = torch.randn(32, device=dev) * 0.1, torch.randn(32, device=dev).abs(), 0.05
+    xd = x.permute(0, 2, 3, 1).reshape(-1, Ci).contiguous()
+    wp = _conv3x3_pack(w)
+    depth = torch.full((frames, oh, ow), float("nan"), device=dev)
+    L.check(lib.vda_output_head(xd.data_ptr(), wp.data_ptr(), b.data_ptr(), hw_.data_ptr(), hb, depth.data_ptr(), frames, ih, iw,
+                                Ci, oh, ow, L.stream_ptr()), "vda_output_head")
+    torch.cuda.synchronize()
+    up = F.interpolate(x.double(), (oh, ow), mode="bilinear", align_corners=True)
+    ref = F.relu(F.conv2d(F.relu(F.conv2d(up, w.double(), b.double(), padding=1)), hw_.double().reshape(1, 32, 1, 1),
+                          torch.tensor([hb], device=dev, dtype=torch.float64)))
+    s = stats(f"head_fused_{Ci}_{oh}x{ow}", depth.reshape(frames, 1, oh, ow), ref)
+    assert s["max_rel_to_peak"] < 2e-3 and s["mean_abs"] < 3e-4 * s["ref_peak"]  # tf32: 10-bit mantissa operands
+    # unfused pair through the C ABI
+    upb = torch.zeros(frames * (oh + 2) * (ow + 2), Ci, device=dev)
+    L.check(lib.vda_bilinear(xd.data_ptr(), L.BF16, upb.data_ptr(), L.F32, frames, ih, iw, 0, oh, ow, 1, Ci, L.stream_ptr()), "bl")
+    ho = torch.zeros(frames * oh * ow, device=dev)
+    run_gemm(L, lib, A=upb, B=wp, lda=Ci, ldb=9 * Ci, rowsA=upb.shape[0], a_dtype=L.F32, b_dtype=L.F32, M=upb.shape[0], N=32, K=Ci,
+             taps=9, ksplit=1, gb=frames, gh=oh, gw=ow, m_padded=1, bias=b, round_bf16=1, out_dtype=L.BF16, out_map=L.MAP_DENSE,
+             head_w=hw_, head_out=ho, head_b=hb, use_tc=1)
+    s2 = stats("head_fused_vs_unfused", depth.reshape(-1), ho)
+    assert s2["max_rel_to_peak"] < 1e-3

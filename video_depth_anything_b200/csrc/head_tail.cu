@@ -1,0 +1,287 @@
+// Fused output head of the bf16 build (dpt_temporal.py:92-97 + dpt.py:118-124):
+//   x[frames, ih, iw, C] bf16 (output_conv1)  --bilinear, align_corners=True, fp32-->  up[frames, oh, ow, C]
+//   --3x3 conv C->32, fp32 weights, tensor cores in TF32 (what cuDNN does for an fp32 conv)--> +bias, ReLU
+//   --1x1 conv 32->1 + bias, ReLU--> depth[frames, oh, ow] fp32.
+// The fp32 `up` tensor (4.4 GB for vitl 518x518) is never materialised: producer warps interpolate each output tile's
+// 18x10-pixel halo straight into shared memory, and the nine taps of the convolution are nine tcgen05.mma descriptors
+// that start at different pixels of that one resident halo tile.
+//
+// Shared-memory layout of the A operand (no swizzle, K-major core matrices): for channel slab s (4 fp32 = 16 bytes)
+// and halo pixel p = hy*10 + hx, the 16 bytes live at s*SLAB + p*16.  A tile row (ty, tx) under tap (dy, dx) is halo
+// pixel (ty+1+dy)*10 + tx+1+dx, i.e. the 128 operand rows are 16 groups of 8 consecutive pixels, groups 160 bytes
+// apart: exactly a UMMA descriptor with SBO = 160, LBO = SLAB and a start address that moves with the tap.
+//
+// Work decomposition: a CTA owns groups of 8 consecutive tiles (8 accumulators of 32 TMEM columns, double-buffered);
+// the channel dimension is walked in chunks of 32 so that one chunk of the weights (9 taps x 32 x 32 fp32 = 36 KB, TMA,
+// 128B swizzle) serves all 8 tiles.  Roles: warps 0-7 interpolate, warp 8 loads weights, warp 9 issues MMAs, warps
+// 10-13 run the epilogue (bias, ReLU, 32->1 dot, ReLU, store).
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tmap.h"
+
+namespace {
+
+constexpr int TH = 16, TW = 8;            // output tile (pixels) == 128 MMA rows
+constexpr int PW = TW + 2;                // halo width
+constexpr int HP = (TH + 2) * PW;         // 180 halo pixels
+constexpr int HPP = 185;                  // padded: slab stride = 16 (mod 128) bytes -> conflict-free stores
+constexpr int SLAB = HPP * 16;            // bytes per 4-channel slab
+constexpr int KC = 32;                    // channels per chunk
+constexpr int ABUF = (KC / 4) * SLAB;     // 23680 B
+constexpr int NABUF = 4;
+constexpr int BBUF = 9 * 4096;            // one chunk of the weights: 9 taps x [32 rows x 128 B]
+constexpr int NBBUF = 2;
+constexpr int GROUP = 8;                  // tiles per accumulator group
+constexpr int NOUT = 32;
+constexpr int OFF_B = 0;
+constexpr int OFF_A = NBBUF * BBUF;
+constexpr int OFF_PAR = OFF_A + NABUF * ABUF;  // bias[32], head_w[32]
+constexpr int OFF_BAR = OFF_PAR + 256;
+constexpr int HT_SMEM = OFF_BAR + 256;
+constexpr int NPROD_WARPS = 8;
+constexpr int HT_THREADS = (NPROD_WARPS + 2 + 4) * 32;
+static_assert(HT_SMEM <= 232448, "shared memory budget");
+static_assert(OFF_A % 1024 == 0, "weight tiles need 1024B alignment");
+
+enum { BA_FULL = 0, BA_EMPTY = NABUF, BB_FULL = 2 * NABUF, BB_EMPTY = 2 * NABUF + NBBUF, BACC_FULL = 2 * NABUF + 2 * NBBUF,
+       BACC_EMPTY = 2 * NABUF + 2 * NBBUF + 2, HT_NBARS = 2 * NABUF + 2 * NBBUF + 4 };
+
+struct HtArgs {
+  const bf16* x;
+  const float* bias;
+  const float* head_w;
+  float* depth;
+  float head_b, rh, rw;
+  int frames, ih, iw, C, oh, ow;
+  int tiles_x, tiles_y, total_tiles, ngroups, nkc;
+};
+
+// K-major, no swizzle: LBO = distance between core matrices along K, SBO = distance between 8-row groups along M.
+__device__ __forceinline__ uint64_t make_noswz_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= 1ull << 46;
+  return d;
+}
+
+__global__ void __launch_bounds__(HT_THREADS, 1)
+head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + HT_NBARS);
+  float* spar = reinterpret_cast<float*>(smem + OFF_PAR);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    if (ptx::smem_u32(smem) & 1023) {
+      printf("vda head_tail: dynamic shared memory is not 1024B aligned\n");
+      __trap();
+    }
+    ptx::prefetch_tmap(&tmW);
+    for (int i = 0; i < NABUF; ++i) {
+      ptx::mbar_init(&bars[BA_FULL + i], NPROD_WARPS);
+      ptx::mbar_init(&bars[BA_EMPTY + i], 1);
+    }
+    for (int i = 0; i < NBBUF; ++i) {
+      ptx::mbar_init(&bars[BB_FULL + i], 1);
+      ptx::mbar_init(&bars[BB_EMPTY + i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&bars[BACC_FULL + i], 1);
+      ptx::mbar_init(&bars[BACC_EMPTY + i], 4);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (threadIdx.x < 64) spar[threadIdx.x] = threadIdx.x < 32 ? a.bias[threadIdx.x] : a.head_w[threadIdx.x - 32];
+  if (warp == NPROD_WARPS + 1) {
+    ptx::tmem_alloc(tmem_slot, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int tiles_per_frame = a.tiles_x * a.tiles_y;
+
+  if (warp < NPROD_WARPS) {
+    // ------------------------------------------------------------------ producers: bilinear halo tile -> smem
+    uint32_t acnt = 0;
+    for (int g = blockIdx.x; g < a.ngroups; g += gridDim.x) {
+      const int nt = min(GROUP, a.total_tiles - g * GROUP);
+      for (int kc = 0; kc < a.nkc; ++kc) {
+        for (int t = 0; t < nt; ++t, ++acnt) {
+          const int ab = acnt % NABUF;
+          ptx::mbar_wait(&bars[BA_EMPTY + ab], ((acnt / NABUF) & 1) ^ 1);
+          const int T = g * GROUP + t;
+          const int f = T / tiles_per_frame, rem = T % tiles_per_frame;
+          const int ty0 = (rem / a.tiles_x) * TH, tx0 = (rem % a.tiles_x) * TW;
+          uint8_t* abuf = smem + OFF_A + ab * ABUF;
+          for (int it = threadIdx.x; it < HP * (KC / 8); it += NPROD_WARPS * 32) {
+            const int p = it >> 2, cg = it & 3;
+            const int hy = p / PW, hx = p - hy * PW;
+            const int oy = ty0 + hy - 1, ox = tx0 + hx - 1;
+            float o[8];
+            if (oy >= 0 && oy < a.oh && ox >= 0 && ox < a.ow) {
+              const float h1r = a.rh * oy;
+              const int h1 = (int)h1r;
+              const int h1p = (h1 < a.ih - 1) ? 1 : 0;
+              const float h1l = h1r - h1, h0l = 1.f - h1l;
+              const float w1r = a.rw * ox;
+              const int w1 = (int)w1r;
+              const int w1p = (w1 < a.iw - 1) ? 1 : 0;
+              const float w1l = w1r - w1, w0l = 1.f - w1l;
+              const bf16* base = a.x + (((long long)f * a.ih + h1) * a.iw + w1) * a.C + kc * KC + cg * 8;
+              float va[8], vb[8], vc[8], vd[8];
+              Vec8<bf16>::load(base, va);
+              Vec8<bf16>::load(base + (long long)w1p * a.C, vb);
+              Vec8<bf16>::load(base + (long long)h1p * a.iw * a.C, vc);
+              Vec8<bf16>::load(base + ((long long)h1p * a.iw + w1p) * a.C, vd);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) o[i] = h0l * (w0l * va[i] + w1l * vb[i]) + h1l * (w0l * vc[i] + w1l * vd[i]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) o[i] = 0.f;  // zero padding of the 3x3 convolution
+            }
+            uint8_t* dst = abuf + (2 * cg) * SLAB + p * 16;
+            *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<float4*>(dst + SLAB) = make_float4(o[4], o[5], o[6], o[7]);
+          }
+          ptx::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&bars[BA_FULL + ab]);
+        }
+      }
+    }
+  } else if (warp == NPROD_WARPS) {
+    // ------------------------------------------------------------------ weight loader (TMA)
+    if (lane == 0) {
+      uint32_t bcnt = 0;
+      for (int g = blockIdx.x; g < a.ngroups; g += gridDim.x) {
+        for (int kc = 0; kc < a.nkc; ++kc, ++bcnt) {
+          const int bb = bcnt % NBBUF;
+          ptx::mbar_wait(&bars[BB_EMPTY + bb], ((bcnt / NBBUF) & 1) ^ 1);
+          ptx::mbar_arrive_expect_tx(&bars[BB_FULL + bb], BBUF);
+          for (int tap = 0; tap < 9; ++tap)
+            ptx::tma_load_2d(smem + OFF_B + bb * BBUF + tap * 4096, &tmW, tap * a.C + kc * KC, 0, &bars[BB_FULL + bb]);
+        }
+      }
+    }
+  } else if (warp == NPROD_WARPS + 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_tf32(128, NOUT);
+      uint32_t acnt = 0, bcnt = 0, gcnt = 0;
+      for (int g = blockIdx.x; g < a.ngroups; g += gridDim.x, ++gcnt) {
+        const int nt = min(GROUP, a.total_tiles - g * GROUP);
+        const int gb = gcnt & 1;
+        ptx::mbar_wait(&bars[BACC_EMPTY + gb], ((gcnt >> 1) & 1) ^ 1);
+        ptx::tc_fence_after();
+        for (int kc = 0; kc < a.nkc; ++kc, ++bcnt) {
+          const int bb = bcnt % NBBUF;
+          ptx::mbar_wait(&bars[BB_FULL + bb], (bcnt / NBBUF) & 1);
+          const uint32_t sb = ptx::smem_u32(smem + OFF_B + bb * BBUF);
+          for (int t = 0; t < nt; ++t, ++acnt) {
+            const int ab = acnt % NABUF;
+            ptx::mbar_wait(&bars[BA_FULL + ab], (acnt / NABUF) & 1);
+            ptx::tc_fence_after();
+            const uint32_t sa = ptx::smem_u32(smem + OFF_A + ab * ABUF);
+            const uint32_t d_tmem = tmem_base + gb * (GROUP * NOUT) + t * NOUT;
+#pragma unroll
+            for (int tap = 0; tap < 9; ++tap) {
+              const uint32_t a0 = sa + ((tap / 3) * PW + (tap % 3)) * 16;  // halo pixel (1+dy, 1+dx), dy,dx = tap/3-1, tap%3-1
+              const uint64_t db = ptx::make_sw128_desc(sb + tap * 4096, 16, 1024);
+#pragma unroll
+              for (int kk = 0; kk < KC / 8; ++kk) {
+                const uint64_t da = make_noswz_desc(a0 + (2 * kk) * SLAB, SLAB, PW * 16);
+                ptx::mma_tf32_ss(d_tmem, da, db + 2 * kk, idesc, (kc | tap | kk) != 0);
+              }
+            }
+            ptx::tc_commit(&bars[BA_EMPTY + ab]);
+          }
+          ptx::tc_commit(&bars[BB_EMPTY + bb]);
+        }
+        ptx::tc_commit(&bars[BACC_FULL + gb]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue: +bias, ReLU, 32->1, +b, ReLU
+    const int q = warp & 3;
+    const int r = q * 32 + lane;          // tile row == TMEM lane == pixel (r / 8, r % 8)
+    const int py = r >> 3, px = r & 7;
+    uint32_t gcnt = 0;
+    for (int g = blockIdx.x; g < a.ngroups; g += gridDim.x, ++gcnt) {
+      const int nt = min(GROUP, a.total_tiles - g * GROUP);
+      const int gb = gcnt & 1;
+      ptx::mbar_wait(&bars[BACC_FULL + gb], (gcnt >> 1) & 1);
+      ptx::tc_fence_after();
+      for (int t = 0; t < nt; ++t) {
+        float v[32];
+        ptx::tmem_ld32(tmem_base + gb * (GROUP * NOUT) + t * NOUT + ((uint32_t)(q * 32) << 16), v);
+        ptx::tmem_ld_wait();
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const float4 b4 = *reinterpret_cast<const float4*>(spar + i), w4 = *reinterpret_cast<const float4*>(spar + 32 + i);
+          s = fmaf(fmaxf(v[i] + b4.x, 0.f), w4.x, s);
+          s = fmaf(fmaxf(v[i + 1] + b4.y, 0.f), w4.y, s);
+          s = fmaf(fmaxf(v[i + 2] + b4.z, 0.f), w4.z, s);
+          s = fmaf(fmaxf(v[i + 3] + b4.w, 0.f), w4.w, s);
+        }
+        s = fmaxf(s + a.head_b, 0.f);
+        const int T = g * GROUP + t;
+        const int f = T / tiles_per_frame, rem = T % tiles_per_frame;
+        const int oy = (rem / a.tiles_x) * TH + py, ox = (rem % a.tiles_x) * TW + px;
+        if (oy < a.oh && ox < a.ow) a.depth[((long long)f * a.oh + oy) * a.ow + ox] = s;
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&bars[BACC_EMPTY + gb]);
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == NPROD_WARPS + 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+extern "C" int vda_output_head(const void* x, const float* w, const float* bias, const float* head_w, float head_b,
+                               float* depth, int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow,
+                               vda_stream_t stream) {
+  VDA_CHECK_ARG(C >= KC && C % KC == 0, "vda_output_head: C=%d must be a multiple of 32", C);
+  VDA_CHECK_ARG(frames > 0 && ih > 0 && iw > 0 && oh > 0 && ow > 0, "vda_output_head: bad geometry");
+  VDA_CHECK_ARG(((uintptr_t)x % 16) == 0 && ((uintptr_t)w % 16) == 0, "vda_output_head: x / w must be 16B aligned");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  CUtensorMap tmW;
+  int rc = vda_make_tmap_2d(&tmW, w, (uint64_t)9 * C, NOUT, (uint64_t)9 * C * 4, 32, NOUT, 4);
+  if (rc) return rc;
+  HtArgs a;
+  a.x = reinterpret_cast<const bf16*>(x);
+  a.bias = bias; a.head_w = head_w; a.depth = depth; a.head_b = head_b;
+  a.rh = oh > 1 ? (float)(ih - 1) / (float)(oh - 1) : 0.f;
+  a.rw = ow > 1 ? (float)(iw - 1) / (float)(ow - 1) : 0.f;
+  a.frames = frames; a.ih = ih; a.iw = iw; a.C = C; a.oh = oh; a.ow = ow;
+  a.tiles_x = (ow + TW - 1) / TW;
+  a.tiles_y = (oh + TH - 1) / TH;
+  a.total_tiles = frames * a.tiles_x * a.tiles_y;
+  a.ngroups = (a.total_tiles + GROUP - 1) / GROUP;
+  a.nkc = C / KC;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t ce = cudaFuncSetAttribute(head_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HT_SMEM);
+    if (ce != cudaSuccess) {
+      vda_set_error("head_tail: cudaFuncSetAttribute(%d) failed: %s", HT_SMEM, cudaGetErrorString(ce));
+      return (int)ce;
+    }
+    attr_set = true;
+  }
+  const int grid = a.ngroups < vda_sm_count() ? a.ngroups : vda_sm_count();
+  head_tail_kernel<<<grid, HT_THREADS, HT_SMEM, st>>>(tmW, a);
+  VDA_CUDA_LAUNCH_CHECK("head_tail_kernel");
+  return 0;
+}

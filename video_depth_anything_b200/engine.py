@@ -142,7 +142,7 @@ class ForwardPlan:
     """Buffers + launch list for `VideoDepthAnything.forward` on x[frames=B*T, 3, H, W] (video_depth.py:58-65)."""
 
     def __init__(self, pw: PackedWeights, batch: int, T: int, H: int, W: int, device, skip_tmp_block=False, use_tc=None,
-                 keep=(), attn_tc=None):
+                 keep=(), attn_tc=None, fused_tail=True):
         assert H % 14 == 0 and W % 14 == 0, f"Input image size {H}x{W} is not a multiple of patch size 14"  # patch_embed.py:73-74
         if T > pw.pe_len:
             raise ValueError(f"video length {T} exceeds the positional-encoding length {pw.pe_len} (num_frames)")
@@ -152,6 +152,7 @@ class ForwardPlan:
         self.dcode = L.BF16 if pw.bf16 else L.F32
         self.use_tc = bool(pw.bf16) if use_tc is None else bool(use_tc)
         self.attn_tc = self.use_tc if attn_tc is None else bool(attn_tc)
+        self.fused_tail = bool(fused_tail)
         self.batch, self.T, self.H, self.W = batch, T, H, W
         self.BT = batch * T
         self.ph, self.pw_ = H // 14, W // 14
@@ -405,16 +406,21 @@ class ForwardPlan:
         # output_conv1 -> bilinear to (14ph, 14pw) -> fp32 island output_conv2 (dpt_temporal.py:91-99)
         o1 = self.buf("oc1", BT * h0 * w0, F // 2)
         self.conv3x3(p1, "oc1.w", h0, w0, F, F // 2, bias=W_["oc1.b"], out=o1, out_map=L.MAP_DENSE)
-        # upsample_bilinear2d is an fp32 op under CUDA autocast: `up` is fp32 and un-rounded in both builds, and so is
-        # everything after it (ori_type is fp32, so `out.to(ori_type)` at dpt_temporal.py:99 is a no-op)
-        up = self.buf("up", BT * (self.H + 2) * (self.W + 2), F // 2, torch.float32, zero=True)
-        self.op(lib.vda_bilinear, o1.data_ptr(), self.dcode, up.data_ptr(), L.F32, BT, h0, w0, 0, self.H, self.W, 1, F // 2)
+        # upsample_bilinear2d is an fp32 op under CUDA autocast: the upsampled map is fp32 and un-rounded in both builds, and
+        # so is everything after it (ori_type is fp32, so `out.to(ori_type)` at dpt_temporal.py:99 is a no-op)
         depth = torch.empty((BT, self.H, self.W), dtype=torch.float32, device=self.device)
         self.bufs["depth"] = depth
-        Mup = BT * (self.H + 2) * (self.W + 2)
-        # fp32 operands: SIMT fp32 FMA in the fp32 build, tcgen05 kind::tf32 in the bf16 build (cuDNN's default for fp32 convs)
-        self.gemm(up, W_["oc2.w32"], Mup, 32, F // 2, taps=9, geo=(BT, self.H, self.W), m_padded=1, bias=W_["oc2.b"],
-                  out_map=L.MAP_DENSE, head_w=W_["oc2.hw"], head_out=depth, head_b=pw.head_b)
+        if self.use_tc and self.fused_tail and (F // 2) % 32 == 0:
+            # bf16 build: interpolation, TF32 tensor-core conv and the ReLU -> 1x1 -> ReLU tail in one kernel
+            self.op(lib.vda_output_head, o1.data_ptr(), W_["oc2.w32"].data_ptr(), W_["oc2.b"].data_ptr(), W_["oc2.hw"].data_ptr(),
+                    float(pw.head_b), depth.data_ptr(), BT, h0, w0, F // 2, self.H, self.W)
+        else:
+            up = self.buf("up", BT * (self.H + 2) * (self.W + 2), F // 2, torch.float32, zero=True)
+            self.op(lib.vda_bilinear, o1.data_ptr(), self.dcode, up.data_ptr(), L.F32, BT, h0, w0, 0, self.H, self.W, 1, F // 2)
+            Mup = BT * (self.H + 2) * (self.W + 2)
+            # fp32 operands: SIMT fp32 FMA in the fp32 build, tcgen05 kind::tf32 in the bf16 build (cuDNN's default for fp32 convs)
+            self.gemm(up, W_["oc2.w32"], Mup, 32, F // 2, taps=9, geo=(BT, self.H, self.W), m_padded=1, bias=W_["oc2.b"],
+                      out_map=L.MAP_DENSE, head_w=W_["oc2.hw"], head_out=depth, head_b=pw.head_b)
         self.depth = depth
 
     # ------------------------------------------------------------------ execution
