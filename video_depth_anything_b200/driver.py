@@ -73,7 +73,7 @@ def shard_windows(n_windows: int, world: int):
 
 
 class WindowedDepthDriver:
-    def __init__(self, model, device="cuda", fp32=False, skip_tmp_block=False, upload_chunk=64):
+    def __init__(self, model, device="cuda", fp32=False, skip_tmp_block=False, upload_chunk=64, distributed=True):
         self.model = model
         self.device = torch.device(device)
         if self.device.type == "cuda" and self.device.index is None:
@@ -82,6 +82,7 @@ class WindowedDepthDriver:
         self.fp32 = fp32
         self.skip_tmp_block = skip_tmp_block
         self.upload_chunk = upload_chunk
+        self.distributed = distributed  # False: ignore an initialised process group (single-rank reference runs)
         self.lib = L.load()
         self.last_scale_shift = None
 
@@ -153,7 +154,7 @@ class WindowedDepthDriver:
         nh, nw = network_size(fh, fw, isz)
         idx = window_index_map(n)
         dist = torch.distributed
-        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        world = dist.get_world_size() if self.distributed and dist.is_available() and dist.is_initialized() else 1
         rank = dist.get_rank() if world > 1 else 0
         first, count = shard_windows(idx.shape[0], world)[rank]
         mine = idx[first:first + count]
