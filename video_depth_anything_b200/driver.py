@@ -12,6 +12,10 @@ runs the cheap sequential stitching pass.  No collective runs inside a forward.
 """
 from __future__ import annotations
 
+import queue
+import threading
+import time
+
 import numpy as np
 import torch
 
@@ -73,7 +77,7 @@ def shard_windows(n_windows: int, world: int):
 
 
 class WindowedDepthDriver:
-    def __init__(self, model, device="cuda", fp32=False, skip_tmp_block=False, upload_chunk=64, distributed=True):
+    def __init__(self, model, device="cuda", fp32=False, skip_tmp_block=False, upload_chunk=64, distributed=True, streaming=True):
         self.model = model
         self.device = torch.device(device)
         if self.device.type == "cuda" and self.device.index is None:
@@ -83,8 +87,10 @@ class WindowedDepthDriver:
         self.skip_tmp_block = skip_tmp_block
         self.upload_chunk = upload_chunk
         self.distributed = distributed  # False: ignore an initialised process group (single-rank reference runs)
+        self.streaming = streaming      # single rank: pipeline upload / forward / stitch / download window by window
         self.lib = L.load()
         self.last_scale_shift = None
+        self.last_stage_s = None
 
     # ------------------------------------------------------------------ stages
     def preprocess(self, frames, ids, nh, nw):
@@ -158,22 +164,154 @@ class WindowedDepthDriver:
         rank = dist.get_rank() if world > 1 else 0
         first, count = shard_windows(idx.shape[0], world)[rank]
         mine = idx[first:first + count]
+        if world == 1 and self.streaming:
+            with torch.cuda.device(self.device), torch.no_grad():
+                return self._run_streaming(frames, n, idx, nh, nw, fh, fw, return_device)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
         with torch.cuda.device(self.device), torch.no_grad():
+            ev[0].record()
             if count > 0:
                 ids = np.unique(mine)
                 rowmap, pre = self.preprocess(frames, ids, nh, nw)
+                ev[1].record()
                 raw = self.forward_windows(pre, rowmap, mine, nh, nw, fh, fw)
                 del pre
             else:
+                ev[1].record()
                 raw = torch.empty((0, fh, fw), dtype=torch.float32, device=self.device)
+            ev[2].record()
             if world > 1:
                 raw = self._gather_raw(raw, idx.shape[0], world, rank, fh, fw)
                 if rank != 0:
                     return None
+            ev[3].record()
             depth = self.stitch(raw, n)
+            ev[4].record()
             if return_device:
                 return depth
-            return depth.cpu().numpy()
+            t0 = time.perf_counter()
+            host = depth.cpu().numpy()
+            # device-side stage times of this call (CUDA events on the launching stream) + the final D2H wall time
+            self.last_stage_s = {"upload_preprocess": ev[0].elapsed_time(ev[1]) / 1e3, "forward_windows": ev[1].elapsed_time(ev[2]) / 1e3,
+                                 "gather": ev[2].elapsed_time(ev[3]) / 1e3, "stitch": ev[3].elapsed_time(ev[4]) / 1e3,
+                                 "d2h": time.perf_counter() - t0}
+            return host
+
+    # ------------------------------------------------------------------ single-rank streaming pipeline
+    def _upload_preprocess(self, frames, lo, hi, pre, nh, nw):
+        """Source frames [lo, hi) -> pre[lo:hi] (pre-processing runs once per source frame)."""
+        fh, fw = frames[0].shape[:2]
+        st = L.stream_ptr()
+        for c0 in range(lo, hi, self.upload_chunk):
+            c1 = min(hi, c0 + self.upload_chunk)
+            if isinstance(frames, np.ndarray) and frames.flags.c_contiguous:
+                host = frames[c0:c1]
+            else:
+                host = np.ascontiguousarray(np.stack([np.asarray(frames[i]) for i in range(c0, c1)]))
+            if host.dtype != np.uint8:
+                raise TypeError("frames must be uint8 [N,H,W,3]")
+            dev = torch.from_numpy(host).to(self.device, non_blocking=True)
+            L.check(self.lib.vda_preprocess_u8(dev.data_ptr(), pre[c0].data_ptr(), c1 - c0, fh, fw, nh, nw, st), "vda_preprocess_u8")
+            del dev
+
+    def _run_streaming(self, frames, n, idx, nh, nw, fh, fw, return_device):
+        """Window k's upload + pre-processing is issued while window k-1 computes (the host copy overlaps the queued
+        kernels), every window is stitched as soon as it is done (the (scale, shift) recurrence is sequential in window
+        order anyway, video_depth.py:379-413), and frames that can no longer change are copied to pinned host memory on
+        a side stream while later windows run.  Same arithmetic, same order, as the batch path."""
+        bf16 = not self.fp32
+        plan = self.model.plan(1, INFER_LEN, nh, nw, self.device, bf16, self.skip_tmp_block)
+        n_win = idx.shape[0]
+        fe = fh * fw
+        total = INFER_LEN + FRAME_STEP * (n_win - 1)
+        s = L.stream_ptr()
+        main = torch.cuda.current_stream()
+        pre = torch.empty((n, 3, nh, nw), dtype=torch.float32, device=self.device)
+        out = torch.empty((total, fh, fw), dtype=torch.float32, device=self.device)
+        raw = torch.empty((2, INFER_LEN, fh, fw), dtype=torch.float32, device=self.device)  # ring: window k -> slot k & 1
+        ref = torch.empty((2, fh, fw), dtype=torch.float32, device=self.device)
+        st_all = torch.zeros((n_win, 2), dtype=torch.float32, device=self.device)
+        st_all[0, 0] = 1.0
+        scratch = torch.zeros(5, dtype=torch.float64, device=self.device)
+        sel_all = torch.as_tensor(idx, dtype=torch.int64).to(self.device)
+        host = None
+        copy_stream = None
+        if not return_device:
+            # device -> pinned staging (cached on the model: page-locking 1 GB costs ~0.5 s) -> the caller's pageable
+            # array, the second hop on a worker thread while the GPU keeps computing
+            host = self._pinned_staging(n * fe * 4).view(torch.float32)[:n * fe].view(n, fh, fw)
+            host_np = host.numpy()
+            result = np.empty((n, fh, fw), dtype=np.float32)
+            copy_stream = torch.cuda.Stream(device=self.device)
+            jobs = queue.Queue()
+
+            def drain():
+                while True:
+                    job = jobs.get()
+                    if job is None:
+                        return
+                    ev, lo, hi = job
+                    ev.synchronize()
+                    np.copyto(result[lo:hi], host_np[lo:hi])
+
+            worker = threading.Thread(target=drain, daemon=True)
+            worker.start()
+        uploaded = 0
+        copied = 0
+        t_begin = time.perf_counter()
+        for k in range(n_win):
+            need = int(idx[k].max()) + 1
+            if need > uploaded:
+                self._upload_preprocess(frames, uploaded, need, pre, nh, nw)
+                uploaded = need
+            cur = raw[k & 1]
+            torch.index_select(pre, 0, sel_all[k], out=plan.x_in)
+            plan.launch()
+            L.check(self.lib.vda_resize_depth(plan.depth.data_ptr(), L.F32, cur.data_ptr(), INFER_LEN, nh, nw, fh, fw, s),
+                    "vda_resize_depth")
+            if k == 0:
+                out[:INFER_LEN].copy_(cur)
+                ref[0].copy_(cur[KEYFRAMES[0]])
+                ref[1].copy_(cur[KEYFRAMES[1]])
+                pos = INFER_LEN
+            else:
+                stp = st_all[k].data_ptr()
+                L.check(self.lib.vda_scale_shift(cur.data_ptr(), ref.data_ptr(), ALIGN_LEN * fe, scratch.data_ptr(), stp, 3, s),
+                        "vda_scale_shift")
+                L.check(self.lib.vda_blend(out[pos - INTERP_LEN].data_ptr(), cur[ALIGN_LEN].data_ptr(), stp, INTERP_LEN, fe, s),
+                        "vda_blend")
+                L.check(self.lib.vda_scale_clamp(cur[OVERLAP].data_ptr(), out[pos].data_ptr(), stp, FRAME_STEP * fe, s),
+                        "vda_scale_clamp")
+                L.check(self.lib.vda_scale_clamp(cur[KEYFRAMES[1]].data_ptr(), ref[1].data_ptr(), stp, fe, s), "vda_scale_clamp")
+                pos += FRAME_STEP
+            if host is not None:
+                final = n if k == n_win - 1 else min(n, pos - INTERP_LEN)  # the last 8 frames are still to be cross-faded
+                if final > copied:
+                    done = torch.cuda.Event()
+                    done.record(main)
+                    copy_stream.wait_event(done)
+                    with torch.cuda.stream(copy_stream):
+                        host[copied:final].copy_(out[copied:final], non_blocking=True)
+                        landed = torch.cuda.Event()
+                        landed.record(copy_stream)
+                    jobs.put((landed, copied, final))
+                    copied = final
+        self.last_scale_shift = st_all
+        if host is None:
+            return out[:n]
+        jobs.put(None)
+        worker.join()
+        main.synchronize()
+        self.last_stage_s = {"streaming_total": time.perf_counter() - t_begin}
+        return result
+
+    def _pinned_staging(self, nbytes):
+        """Page-locked staging buffer, cached on the model and grown on demand."""
+        buf = getattr(self.model, "_vda_pinned_staging", None)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty((nbytes,), dtype=torch.uint8, pin_memory=True)
+            self.model._vda_pinned_staging = buf
+        return buf
 
     def _gather_raw(self, raw, n_win, world, rank, fh, fw):
         return gather_window_blocks(raw, n_win, world, rank)
