@@ -165,6 +165,155 @@ __global__ void __launch_bounds__(256) temporal_attn_kernel(const T* __restrict_
   }
 }
 
+
+// ---------------------------------------------------------------- temporal attention, bf16 build, warp-level MMA
+// One warp per (token, head): Q, K, V (T x d bf16 each) are staged in shared memory with row-contiguous 16-byte loads,
+// S = Q K^T and O = P V run on mma.sync.m16n8k16 (the problem is 32 x 32 x d -- far too small for a tcgen05 tile, and
+// on fp32 FMAs it is issue-bound at ~4x the memory time), the softmax works on the accumulator fragments with quad
+// shuffles, P never leaves registers (accumulator layout == A-operand layout), O goes back through shared memory so
+// that global stores are row-contiguous.  Rounding points as in the SIMT kernel: scores -> bf16, softmax fp32,
+// probabilities -> bf16, output -> bf16 (motion_module/attention.py:187-207 under autocast).
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void mma16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+template <int TT>
+__global__ void __launch_bounds__(128) temporal_attn_mma_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ o, int hw,
+                                                                int C, int heads, int d, float scale, int items) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  constexpr int NT = TT / 8;   // score n-tiles (keys)
+  constexpr int MT = TT / 16;  // m-tiles (queries)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int item = blockIdx.x * (blockDim.x >> 5) + warp;  // (b, p, h)
+  if (item >= items) return;
+  const int h = item % heads;
+  const int bp = item / heads;
+  const int b = bp / hw, p = bp % hw;
+  const int pitch = 2 * d + 16;  // bytes per staged row: 16 B of padding keeps ldmatrix conflict-free
+  uint8_t* Qs = smem_raw + (size_t)warp * 3 * TT * pitch;
+  uint8_t* Ks = Qs + TT * pitch;
+  uint8_t* Vs = Ks + TT * pitch;
+  const long long ld = 3LL * C;
+  const int vpr = d >> 3;  // 16-byte vectors per row
+  for (int i = lane; i < TT * vpr; i += 32) {
+    const int t = i / vpr, c = i - t * vpr;
+    const bf16* rp = qkv + (((long long)b * TT + t) * hw + p) * ld + h * d + c * 8;
+    *reinterpret_cast<uint4*>(Qs + t * pitch + c * 16) = *reinterpret_cast<const uint4*>(rp);
+    *reinterpret_cast<uint4*>(Ks + t * pitch + c * 16) = *reinterpret_cast<const uint4*>(rp + C);
+    *reinterpret_cast<uint4*>(Vs + t * pitch + c * 16) = *reinterpret_cast<const uint4*>(rp + 2 * C);
+  }
+  __syncwarp();
+  const uint32_t qs = (uint32_t)__cvta_generic_to_shared(Qs), ks = (uint32_t)__cvta_generic_to_shared(Ks),
+                 vs = (uint32_t)__cvta_generic_to_shared(Vs);
+  const int g = lane >> 2, tq = lane & 3;
+  // ldmatrix lane -> row / column-half assignments
+  const int a_row = lane & 15, a_col = (lane >> 4) * 16;                       // A: 16 rows x (2 x 8 cols)
+  const int b_row = (lane & 7) + ((lane >> 4) << 3), b_col = ((lane >> 3) & 1) * 16;  // B (two n-tiles): [n][k]
+  const int v_row = (lane & 7) + (((lane >> 3) & 1) << 3), v_col = (lane >> 4) * 16;   // V^T (two n-tiles): [k][n]
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) {
+    float sc[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) sc[n][0] = sc[n][1] = sc[n][2] = sc[n][3] = 0.f;
+    for (int k0 = 0; k0 < d; k0 += 16) {
+      uint32_t a[4];
+      ldsm_x4(qs + (mt * 16 + a_row) * pitch + k0 * 2 + a_col, a[0], a[1], a[2], a[3]);
+#pragma unroll
+      for (int n2 = 0; n2 < NT / 2; ++n2) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4(ks + (n2 * 16 + b_row) * pitch + k0 * 2 + b_col, b0, b1, b2, b3);
+        mma16816(sc[2 * n2], a, b0, b1);
+        mma16816(sc[2 * n2 + 1], a, b2, b3);
+      }
+    }
+    // rows g and g + 8 of this m-tile: scores -> bf16, softmax in fp32 over the quad, probabilities -> bf16
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) sc[n][i] = round_bf16(scale * sc[n][i]);
+      mx0 = fmaxf(mx0, fmaxf(sc[n][0], sc[n][1]));
+      mx1 = fmaxf(mx1, fmaxf(sc[n][2], sc[n][3]));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+      sc[n][0] = expf(sc[n][0] - mx0);
+      sc[n][1] = expf(sc[n][1] - mx0);
+      sc[n][2] = expf(sc[n][2] - mx1);
+      sc[n][3] = expf(sc[n][3] - mx1);
+      s0 += sc[n][0] + sc[n][1];
+      s1 += sc[n][2] + sc[n][3];
+    }
+    s0 += __shfl_xor_sync(0xffffffffu, s0, 1);
+    s0 += __shfl_xor_sync(0xffffffffu, s0, 2);
+    s1 += __shfl_xor_sync(0xffffffffu, s1, 1);
+    s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
+    uint32_t pa[NT / 2][4];  // P as A fragments: k-step n2 covers keys 16 n2 .. 16 n2 + 15
+#pragma unroll
+    for (int n2 = 0; n2 < NT / 2; ++n2) {
+      pa[n2][0] = pack_bf16x2(sc[2 * n2][0] / s0, sc[2 * n2][1] / s0);
+      pa[n2][1] = pack_bf16x2(sc[2 * n2][2] / s1, sc[2 * n2][3] / s1);
+      pa[n2][2] = pack_bf16x2(sc[2 * n2 + 1][0] / s0, sc[2 * n2 + 1][1] / s0);
+      pa[n2][3] = pack_bf16x2(sc[2 * n2 + 1][2] / s1, sc[2 * n2 + 1][3] / s1);
+    }
+    // O = P V, 16 output columns at a time; written into the (already consumed) Q rows of this m-tile
+    for (int n0 = 0; n0 < d; n0 += 16) {
+      float oc[2][4] = {};
+#pragma unroll
+      for (int n2 = 0; n2 < NT / 2; ++n2) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_t(vs + (n2 * 16 + v_row) * pitch + n0 * 2 + v_col, b0, b1, b2, b3);
+        mma16816(oc[0], pa[n2], b0, b1);
+        mma16816(oc[1], pa[n2], b2, b3);
+      }
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        *reinterpret_cast<uint32_t*>(Qs + (mt * 16 + g) * pitch + (n0 + j * 8 + tq * 2) * 2) = pack_bf16x2(oc[j][0], oc[j][1]);
+        *reinterpret_cast<uint32_t*>(Qs + (mt * 16 + g + 8) * pitch + (n0 + j * 8 + tq * 2) * 2) = pack_bf16x2(oc[j][2], oc[j][3]);
+      }
+    }
+  }
+  __syncwarp();
+  for (int i = lane; i < TT * vpr; i += 32) {
+    const int t = i / vpr, c = i - t * vpr;
+    *reinterpret_cast<uint4*>(o + (((long long)b * TT + t) * hw + p) * C + h * d + c * 8) =
+        *reinterpret_cast<const uint4*>(Qs + t * pitch + c * 16);
+  }
+}
+
+template <int TT>
+int launch_temporal_mma(const void* qkv, void* o, int batch, int hw, int C, int heads, cudaStream_t st) {
+  const int d = C / heads;
+  const int pitch = 2 * d + 16;
+  const int wpb = 4;
+  const size_t smem = (size_t)wpb * 3 * TT * pitch;
+  auto kern = temporal_attn_mma_kernel<TT>;
+  if (smem > 48 * 1024) {
+    cudaError_t ce = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (ce != cudaSuccess) {
+      vda_set_error("temporal_attn_mma: smem attribute %zu failed: %s", smem, cudaGetErrorString(ce));
+      return (int)ce;
+    }
+  }
+  const int items = batch * hw * heads;
+  kern<<<(items + wpb - 1) / wpb, wpb * 32, smem, st>>>((const bf16*)qkv, (bf16*)o, hw, C, heads, d, 1.0f / sqrtf((float)d), items);
+  VDA_CUDA_LAUNCH_CHECK("temporal_attn_mma_kernel");
+  return 0;
+}
+
 template <typename T, int TT, bool RB>
 int launch_temporal(const void* qkv, void* o, int batch, int hw, int C, int heads, cudaStream_t st) {
   const int d = C / heads;
@@ -212,6 +361,12 @@ extern "C" int vda_temporal_attention(const void* qkv, void* o, int32_t dtype, i
   VDA_CHECK_ARG(heads <= 8 && (heads & (heads - 1)) == 0, "vda_temporal_attention: heads must be 1,2,4,8");
   const bool bf = dtype == VDA_BF16 && round_bf16, f32 = dtype == VDA_F32 && !round_bf16;
   VDA_CHECK_ARG(bf || f32, "vda_temporal_attention: unsupported dtype/rounding combination");
+  const int dd = C / heads;
+  if (bf && dd % 16 == 0 && dd <= 128 && (T == 16 || T == 32 || T == 64)) {
+    if (T == 16) return launch_temporal_mma<16>(qkv, o, batch, hw, C, heads, st);
+    if (T == 32) return launch_temporal_mma<32>(qkv, o, batch, hw, C, heads, st);
+    return launch_temporal_mma<64>(qkv, o, batch, hw, C, heads, st);
+  }
 #define TA(TT)                                                                              \
   return bf ? launch_temporal<bf16, TT, true>(qkv, o, batch, hw, C, heads, st)              \
             : launch_temporal<float, TT, false>(qkv, o, batch, hw, C, heads, st)
