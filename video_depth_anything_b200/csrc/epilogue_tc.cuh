@@ -71,9 +71,36 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
   const int act = GEN ? e.act : (EK == EK_GELU ? (int)VDA_ACT_GELU : (int)VDA_ACT_NONE);
   const bool has_resid = GEN ? (e.resid != nullptr) : (EK == EK_RESID);
   const bool has_out = GEN ? (e.out != nullptr) : (EK != EK_RESID);
-  const bool has_res = GEN && e.res != nullptr, has_res2 = GEN && e.res2 != nullptr, has_relu = GEN && e.out_relu != nullptr;
+  // skip connections / relu copy only exist on the generic, non-GEGLU kind
+  const bool has_res = GEN && !GEGLU && e.res != nullptr, has_res2 = GEN && !GEGLU && e.res2 != nullptr;
+  const bool has_relu = GEN && e.out_relu != nullptr;
   const bool assign = GEN && e.resid_assign;
   uint32_t pk[32];
+  // phase-2 coordinates of this lane: 8 output columns, rows 4 t + lane / 8
+  const int j = lane & 7;
+  const int col = (GEGLU ? ((n0 + c) >> 1) : (n0 + c)) + 8 * j;  // first of this lane's 8 output columns
+  int ocol = col;
+  int row_add = 0;
+  if (e.out_map == VDA_MAP_CONVT) {
+    const int kk = col / e.ct_cout;
+    ocol = col - kk * e.ct_cout;
+    row_add = (kk / e.ct_k) * (e.gw * e.ct_k + 2) + (kk % e.ct_k);
+  }
+  // skip connections: fetch this lane's phase-2 operands now, so that their latency hides behind phase 1
+  uint4 rv[(GEN && !GEGLU) ? 8 : 1], rv2[(GEN && !GEGLU) ? 8 : 1];
+  if constexpr (GEN && !GEGLU) {
+    if (has_res) {
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        const int rr = 4 * t + (lane >> 3);
+        const int orow = __shfl_sync(0xffffffffu, ri.out_row, rr);
+        const int rrow = __shfl_sync(0xffffffffu, ri.res_row, rr);
+        rv[t] = make_uint4(0, 0, 0, 0);
+        if (orow >= 0)
+          rv[t] = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.res) + (long long)rrow * e.ldres + ocol);
+      }
+    }
+  }
   // ---------------------------------------------------------------- phase 1
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
@@ -123,21 +150,25 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
   }
   __syncwarp();
   // ---------------------------------------------------------------- phase 2
-  const int j = lane & 7;
-  const int col = (GEGLU ? ((n0 + c) >> 1) : (n0 + c)) + 8 * j;  // first of this lane's 8 output columns
-  int ocol = col;
-  int row_add = 0;
-  if (e.out_map == VDA_MAP_CONVT) {
-    const int kk = col / e.ct_cout;
-    ocol = col - kk * e.ct_cout;
-    row_add = (kk / e.ct_k) * (e.gw * e.ct_k + 2) + (kk % e.ct_k);
-  }
   float gam[8];
   if (has_resid && !assign) {
     const float4 g0 = *reinterpret_cast<const float4*>(e.gamma + col), g1 = *reinterpret_cast<const float4*>(e.gamma + col + 4);
     gam[0] = g0.x; gam[1] = g0.y; gam[2] = g0.z; gam[3] = g0.w; gam[4] = g1.x; gam[5] = g1.y; gam[6] = g1.z; gam[7] = g1.w;
   }
-#pragma unroll(GEN ? 2 : 8)
+  if constexpr (GEN && !GEGLU) {
+    if (has_res2) {  // second skip connection: all eight loads in flight before the first use (pk[] is dead by now)
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        const int rr = 4 * t + (lane >> 3);
+        const int orow = __shfl_sync(0xffffffffu, ri.out_row, rr);
+        const int rrow = __shfl_sync(0xffffffffu, ri.res_row, rr);
+        rv2[t] = make_uint4(0, 0, 0, 0);
+        if (orow >= 0)
+          rv2[t] = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.res2) + (long long)rrow * e.ldres + ocol);
+      }
+    }
+  }
+#pragma unroll
   for (int t = 0; t < 8; ++t) {
     const int rr = 4 * t + (lane >> 3);
     const uint4 p = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((j ^ (rr & 7)) << 4));
@@ -175,17 +206,23 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
       }
       if (!has_out) continue;
     }
-    if (has_res) {
-      float r8[8];
-      Vec8<bf16>::load(reinterpret_cast<const bf16*>(e.res) + (long long)rrow * e.ldres + ocol, r8);
+    if constexpr (GEN && !GEGLU) {
+      if (has_res) {
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(&rv[t]);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) v[k] = round_bf16(v[k] + r8[k]);
-    }
-    if (has_res2) {
-      float r8[8];
-      Vec8<bf16>::load(reinterpret_cast<const bf16*>(e.res2) + (long long)rrow * e.ldres + ocol, r8);
+        for (int k = 0; k < 4; ++k) {
+          v[2 * k] = round_bf16(v[2 * k] + bf16lo_to_f32(w[k]));
+          v[2 * k + 1] = round_bf16(v[2 * k + 1] + bf16hi_to_f32(w[k]));
+        }
+      }
+      if (has_res2) {
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(&rv2[t]);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) v[k] = round_bf16(v[k] + r8[k]);
+        for (int k = 0; k < 4; ++k) {
+          v[2 * k] = round_bf16(v[2 * k] + bf16lo_to_f32(w[k]));
+          v[2 * k + 1] = round_bf16(v[2 * k + 1] + bf16hi_to_f32(w[k]));
+        }
+      }
     }
     const long long oo = (long long)(orow + row_add) * e.ldo + ocol;
     Vec8<bf16>::store(reinterpret_cast<bf16*>(e.out) + oo, v);

@@ -262,6 +262,7 @@ int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
   VDA_CHECK_ARG(((uintptr_t)d->A % 16) == 0 && ((uintptr_t)d->B % 16) == 0, "vda_gemm(tc): operands must be 16B aligned");
   VDA_CHECK_ARG(d->act != VDA_ACT_GEGLU || d->N % 64 == 0, "vda_gemm(tc): GEGLU needs N %% 64 == 0");
   VDA_CHECK_ARG(d->head_w == nullptr || d->N == 32, "vda_gemm(tc): fused head needs N == 32");
+  VDA_CHECK_ARG(d->act != VDA_ACT_GEGLU || (d->res == nullptr && d->res2 == nullptr), "vda_gemm(tc): GEGLU has no skip inputs");
   if (tf32) {
     // the fp32 island of the bf16 build (dpt_temporal.py:95-97): fp32 operands through kind::tf32, as cuDNN does by default
     VDA_CHECK_ARG(d->N <= 32, "vda_gemm(tc, tf32): only the N <= 32 output head is instantiated");

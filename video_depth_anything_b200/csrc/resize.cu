@@ -8,17 +8,13 @@ namespace {
 // value = h0*(w0*a + w1*b) + h1*(w0*c + w1*d), computed in fp32 and rounded once to the storage type.
 template <typename T, typename TO>
 __global__ void __launch_bounds__(256) bilinear_kernel(const T* __restrict__ in, TO* __restrict__ out, int ih, int iw,
-                                                      int ipad, int oh, int ow, int opad, int C, float rh, float rw,
-                                                      long long total_vec) {
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= total_vec) return;
+                                                      int ipad, int oh, int ow, int opad, int C, float rh, float rw) {
+  // grid = (x-chunks, oh, frames): the row quantities are block-uniform and no 64-bit division is needed
   const int nv = C >> 3;
-  const int cv = (int)(idx % nv);
-  long long pix = idx / nv;
-  const int ox = (int)(pix % ow);
-  pix /= ow;
-  const int oy = (int)(pix % oh);
-  const int f = (int)(pix / oh);
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= ow * nv) return;
+  const int ox = idx / nv, cv = idx - ox * nv;
+  const int oy = blockIdx.y, f = blockIdx.z;
   const float h1r = rh * oy;
   const int h1 = (int)h1r;
   const int h1p = (h1 < ih - 1) ? 1 : 0;
@@ -114,10 +110,10 @@ extern "C" int vda_bilinear(const void* in, int32_t in_dtype, void* out, int32_t
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const float rh = oh > 1 ? (float)(ih - 1) / (float)(oh - 1) : 0.f;
   const float rw = ow > 1 ? (float)(iw - 1) / (float)(ow - 1) : 0.f;
-  const long long total = (long long)frames * oh * ow * (C / 8);
-  const unsigned grid = (unsigned)((total + 255) / 256);
+  VDA_CHECK_ARG(oh <= 65535 && frames <= 65535, "vda_bilinear: oh / frames exceed the grid limits");
+  const dim3 grid((unsigned)((ow * (C / 8) + 255) / 256), (unsigned)oh, (unsigned)frames);
   const int ip = in_padded ? 1 : 0, op = out_padded ? 1 : 0;
-#define BL(TI, TO) bilinear_kernel<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, (TO*)out, ih, iw, ip, oh, ow, op, C, rh, rw, total)
+#define BL(TI, TO) bilinear_kernel<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, (TO*)out, ih, iw, ip, oh, ow, op, C, rh, rw)
   if (in_dtype == VDA_BF16 && out_dtype == VDA_BF16) BL(bf16, bf16);
   else if (in_dtype == VDA_BF16 && out_dtype == VDA_F32) BL(bf16, float);
   else if (in_dtype == VDA_F32 && out_dtype == VDA_F32) BL(float, float);
