@@ -276,7 +276,9 @@ int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
   // small problems: prefer more tiles over wide tiles so every SM gets work
   if (bn == 256 && (int64_t)((d->M + 127) / 128) * ((d->N + 255) / 256) < vda_sm_count()) bn = 128;
   // large contractions: CTA pairs (256 x 256 tile per pair, half the B traffic per SM)
-  if (bn == 256 && pair_enabled() && (int64_t)((d->M + 255) / 256) * ((d->N + 255) / 256) >= vda_sm_count() / 2)
+  // (short contractions are epilogue / HBM bound and run better without the pair's lock-step)
+  if (bn == 256 && pair_enabled() && (int64_t)d->K * d->taps * d->ksplit >= 512 &&
+      (int64_t)((d->M + 255) / 256) * ((d->N + 255) / 256) >= vda_sm_count() / 2)
     return vda_gemm_tc_pair(d, st);
   switch (bn) {
     case 32: return launch_tc<32, bf16, true, false>(d, st);

@@ -18,16 +18,20 @@
 namespace {
 
 constexpr int BM = 128, BK = 64, BN = 256;  // per-CTA accumulator: 128 x 256; pair tile 256 x 256
-constexpr int NUM_EPI_WARPS = 8;
-constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
 constexpr int A_BYTES = BM * BK * 2;          // 16 KB: this CTA's rows of A
 constexpr int B_BYTES = (BN / 2) * BK * 2;    // 16 KB: this CTA's half of the B tile
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int STAGES = 6;
-constexpr int EPI_BYTES = NUM_EPI_WARPS * 4096 + 2 * BN * 4;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 256;
 constexpr int TMEM_COLS = 2 * BN;
-static_assert(SMEM_BYTES <= 232448, "shared memory budget exceeded");
+// Epilogue warps: 8 by default; the GELU kind (mlp.fc1: ~18 instructions per element against 8192 MMA cycles per tile)
+// is epilogue-bound with 2 warps per scheduler, so it runs 16 (one 64-column chunk per warp and tile) and gives up a stage.
+template <int EK> struct PairCfg {
+  static constexpr int NUM_EPI_WARPS = (EK == EK_GELU) ? 16 : 8;
+  static constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
+  static constexpr int STAGES = (EK == EK_GELU) ? 5 : 6;
+  static constexpr int EPI_BYTES = NUM_EPI_WARPS * 4096 + 2 * BN * 4;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 256;
+  static_assert(SMEM_BYTES <= 232448, "shared memory budget exceeded");
+};
 
 struct Tc2Args {
   int M, N, K;
@@ -36,9 +40,11 @@ struct Tc2Args {
 };
 
 template <int EK>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PairCfg<EK>::NUM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Tc2Args a,
                 const Epi e) {
+  constexpr int NUM_EPI_WARPS = PairCfg<EK>::NUM_EPI_WARPS, STAGES = PairCfg<EK>::STAGES, EPI_BYTES = PairCfg<EK>::EPI_BYTES;
+  constexpr int NGROUPS = NUM_EPI_WARPS / 4;  // column groups: warps of one group cover the four TMEM lane quadrants
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* epi_smem = smem + STAGES * STAGE_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + EPI_BYTES);
@@ -138,7 +144,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ------------------------------------------------------------------ epilogue warps (both CTAs, own accumulator half)
     const int ew = warp - 2;
     const int q = warp & 3;
-    const int half = ew >> 2;
+    const int grp = ew >> 2;
     const int et = threadIdx.x - 64;
     const bool geglu = (EK == EK_GENERIC) ? (e.act == VDA_ACT_GEGLU) : (EK == EK_GEGLU);
     const int cw = geglu ? 128 : 64;
@@ -159,7 +165,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const int m = m0 + q * 32 + lane;
       const RowIdx ri = make_row_idx(e, m);
       const uint32_t trow = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
-      for (int c = half * cw; c < BN; c += 2 * cw) {
+      for (int c = grp * cw; c < BN; c += NGROUPS * cw) {
         if (n0 + c >= a.N) break;
         if (c + cw <= BN && epi_fast_ok(e, n0 + c)) {
           if constexpr (EK == EK_GENERIC) {
@@ -213,14 +219,14 @@ int launch_tc2(const vda_gemm_desc* d, cudaStream_t st) {
   auto kern = gemm_tc2_kernel<EK>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t ce = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    cudaError_t ce = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg<EK>::SMEM_BYTES);
     if (ce != cudaSuccess) {
-      vda_set_error("gemm_tc2: cudaFuncSetAttribute(%d) failed: %s", SMEM_BYTES, cudaGetErrorString(ce));
+      vda_set_error("gemm_tc2: cudaFuncSetAttribute(%d) failed: %s", PairCfg<EK>::SMEM_BYTES, cudaGetErrorString(ce));
       return (int)ce;
     }
     attr_set = true;
   }
-  kern<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(tmA, tmB, a, e);
+  kern<<<grid, PairCfg<EK>::NUM_THREADS, PairCfg<EK>::SMEM_BYTES, st>>>(tmA, tmB, a, e);
   VDA_CUDA_LAUNCH_CHECK("gemm_tc2_kernel");
   return 0;
 }
