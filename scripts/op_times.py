@@ -31,7 +31,6 @@ def main():
     plan.x_in.normal_()
     lib = plan._lib
     st = L.stream_ptr()
-    names = {getattr(lib, n): n for n in dir(lib) if n.startswith("vda_")} if hasattr(lib, "__dir__") else {}
     for _ in range(2):
         plan.launch()
     torch.cuda.synchronize()

@@ -1,19 +1,25 @@
 // tcgen05 flash attention for the DINOv2 encoder (dinov2_layers/attention.py:49-59), head_dim 64, non-causal.
 //
-// One CTA = up to 256 query rows (two 128-row tiles) of one (frame, head); one CTA per SM.  The two tiles ping-pong:
-// while softmax group 0 works on its S tile the tensor core computes the other tile's S / PV.
-//   warp 0     : TMA producer (Q tiles once, then K_j / V_j tiles of 128 keys through 3-stage rings)
-//   warp 1     : MMA issuer;  S_t = Q_t K_j^T (128x128x64) and PV_t = P_t V_j (128x64x128), accumulators in TMEM
-//   warps 2-9  : softmax group 0 (tile 0): one query row x 64 keys per thread (TMEM lane == row; two warps per lane
-//                quadrant split the 128 keys of a block and exchange the block max through shared memory)
-//   warps 10-17: softmax group 1 (tile 1)
-// A softmax thread reads its S row out of TMEM ONCE, rounding to bf16 and packing as it goes (64 registers), releases
-// the TMEM tile immediately (the next S MMA overlaps the exponentials), then: online max / sum in fp32, P written to
-// shared memory as the bf16 A operand of the PV MMA, O accumulated in TMEM across key blocks (rescaled lazily, only
-// when the running max moves by more than 2^8).
+// One CTA = up to 256 query rows (two 128-row tiles) of one (frame, head); one CTA per SM.  The work of a CTA is cut
+// into FOUR independent streams (tile t, key half hh): stream (t, hh) runs an online softmax of tile t's rows over the
+// keys [128 j + 64 hh, +64) of every key block j, with its own S and O accumulators in TMEM, its own running max / sum
+// and its own MMA issuer, and the two halves of a tile are merged once, at the end (a two-way split-KV).
+//   warp 0      : TMA producer (Q tiles once, then K_j / V_j tiles of 128 keys through 3-stage rings)
+//   warps 1-4   : MMA issuer of stream w-1 (one thread each): S = Q_t K_j[hh]^T (128x64x64), O += P V_j[hh] (128x64x64)
+//   warps 5-20  : softmax, four warps per stream (one per TMEM lane quadrant); a thread owns one query row x 64 keys
+// Why streams: a softmax warp's iteration is a CHAIN of waits (S ready -> TMEM read -> max -> 64 exponentials -> PV
+// done -> P store), and the exponentials (MUFU.EX2, 4 lanes/clk/scheduler: scripts/micro/xu_pipe.cu) are the busiest
+// unit.  With one issuer and an exchange of the row max between the key halves (the previous version) the sixteen
+// warps ran in lock step -- all four warps of a scheduler queued on the MUFU together, then left it idle together
+// (per-phase clock64 trace: 1750 clk in the exponentials with ~3.4 warps contending, 1750 clk outside them).
+// Independent streams have no per-block exchange and no in-order issue coupling, so they drift apart and one stream's
+// exponentials run under the others' waits.
+// A softmax thread reads its 64 scores out of TMEM ONCE, rounding to bf16 and packing as it goes (32 registers),
+// releases the S tile immediately (the next S MMA overlaps the exponentials), then: online max / sum in fp32, P
+// written to shared memory as the bf16 A operand of the PV MMA, O accumulated in TMEM across key blocks (rescaled
+// lazily, only when the running max moves by more than 2^8).
 // Tried and dropped: evaluating half of the exponentials with a Cody-Waite + cubic polynomial on the FMA pipe (the
-// FlashAttention-4 trick) made the kernel 12 % slower -- it is instruction-issue bound (IPC 0.44 per scheduler with
-// ~7 instructions per score), not MUFU bound (XU pipe 44 %).
+// FlashAttention-4 trick): 12 % slower, the FMA pipe and the issue slots are nearly as loaded as the MUFU.
 // Numerics follow autocast: scores are rounded to bf16 (q@k^T is a bf16 tensor; the 2^-3 scale commutes with the
 // rounding), softmax runs in fp32, probabilities are rounded to bf16 before P@V, the output is rounded to bf16.
 #include "common.cuh"
@@ -22,18 +28,19 @@
 
 namespace {
 
-constexpr int BQ = 128, BKV = 128, HD = 64;
+constexpr int BQ = 128, BKV = 128, HD = 64, KH = 64;  // KH: keys per stream and block
 constexpr int NS = 3;                  // K / V ring depth
 constexpr int TILE_BYTES = 128 * 128;  // 128 rows x 64 bf16
 constexpr int OFF_Q = 0;                         // 2 tiles
 constexpr int OFF_K = 2 * TILE_BYTES;            // NS tiles
 constexpr int OFF_V = OFF_K + NS * TILE_BYTES;   // NS tiles
-constexpr int OFF_P = OFF_V + NS * TILE_BYTES;   // 2 x (2 atoms of 128 rows x 64 keys)
+constexpr int OFF_P = OFF_V + NS * TILE_BYTES;   // 4 streams x (128 rows x 64 keys)
 constexpr int OFF_BAR = OFF_P + 4 * TILE_BYTES;
-constexpr int OFF_X = OFF_BAR + 256;             // block-max / row-sum exchange between partner warps: 6 KB
-constexpr int FA_SMEM = OFF_X + 6 * 1024;
-constexpr int FA_THREADS = 64 + 512;
-constexpr uint32_t TM_S = 0, TM_O = 256, TM_COLS = 512;  // S_t at TM_S + 128 t, O_t at TM_O + 64 t
+constexpr int OFF_X = OFF_BAR + 256;             // (max, sum) exchange between the two halves of a tile: 4 KB
+constexpr int FA_SMEM = OFF_X + 4 * 1024;
+constexpr int FA_WARPS = 1 + 4 + 16;
+constexpr int FA_THREADS = FA_WARPS * 32;
+constexpr uint32_t TM_S = 0, TM_O = 256, TM_COLS = 512;  // S of stream s at TM_S + 64 s, O at TM_O + 64 s
 
 // barrier indices
 constexpr int B_QFULL = 0;               // 1
@@ -41,11 +48,11 @@ constexpr int B_KFULL = 1;               // NS
 constexpr int B_KEMPTY = B_KFULL + NS;   // NS
 constexpr int B_VFULL = B_KEMPTY + NS;   // NS
 constexpr int B_VEMPTY = B_VFULL + NS;   // NS
-constexpr int B_SFULL = B_VEMPTY + NS;   // 2
-constexpr int B_SFREE = B_SFULL + 2;     // 2
-constexpr int B_PFULL = B_SFREE + 2;     // 2
-constexpr int B_PVDONE = B_PFULL + 2;    // 2
-constexpr int NBARS = B_PVDONE + 2;
+constexpr int B_SFULL = B_VEMPTY + NS;   // 4
+constexpr int B_SFREE = B_SFULL + 4;     // 4
+constexpr int B_PFULL = B_SFREE + 4;     // 4
+constexpr int B_PVDONE = B_PFULL + 4;    // 4
+constexpr int NBARS = B_PVDONE + 4;
 static_assert(NBARS * 8 + 8 <= 256, "barrier area");
 static_assert(FA_SMEM <= 232448, "shared memory budget");
 
@@ -81,15 +88,15 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
     ptx::mbar_init(&bars[B_QFULL], 1);
     for (int s = 0; s < NS; ++s) {
       ptx::mbar_init(&bars[B_KFULL + s], 1);
-      ptx::mbar_init(&bars[B_KEMPTY + s], 1);
+      ptx::mbar_init(&bars[B_KEMPTY + s], 2 * ntiles);  // one commit per active stream
       ptx::mbar_init(&bars[B_VFULL + s], 1);
-      ptx::mbar_init(&bars[B_VEMPTY + s], 1);
+      ptx::mbar_init(&bars[B_VEMPTY + s], 2 * ntiles);
     }
-    for (int t = 0; t < 2; ++t) {
-      ptx::mbar_init(&bars[B_SFULL + t], 1);
-      ptx::mbar_init(&bars[B_SFREE + t], 8);
-      ptx::mbar_init(&bars[B_PFULL + t], 8);
-      ptx::mbar_init(&bars[B_PVDONE + t], 1);
+    for (int s = 0; s < 4; ++s) {
+      ptx::mbar_init(&bars[B_SFULL + s], 1);
+      ptx::mbar_init(&bars[B_SFREE + s], 4);
+      ptx::mbar_init(&bars[B_PFULL + s], 4);
+      ptx::mbar_init(&bars[B_PVDONE + s], 1);
     }
     ptx::fence_barrier_init();
   }
@@ -119,24 +126,24 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         ptx::tma_load_2d(smem + OFF_V + s * TILE_BYTES, &tm, 2 * D + h * HD, row0 + j * BKV, &bars[B_VFULL + s]);
       }
     }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = ptx::make_idesc_bf16(BQ, BKV, 0, 0);
+  } else if (warp <= 4) {
+    // ------------------------------------------------------------------ MMA issuer of stream warp-1
+    const int sid = warp - 1, t = sid >> 1, hh = sid & 1;
+    if (lane == 0 && t < ntiles) {
+      constexpr uint32_t idesc_s = ptx::make_idesc_bf16(BQ, KH, 0, 0);
       constexpr uint32_t idesc_pv = ptx::make_idesc_bf16(BQ, HD, 0, 1);  // B = V is MN-major (d contiguous)
-      auto issue_s = [&](int j) {  // S_t(j) for every tile; frees the K stage when done
+      const uint64_t dq = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_Q + t * TILE_BYTES), 16, 1024);
+      const uint64_t dp = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_P + sid * TILE_BYTES), 16, 1024);
+      const uint32_t ds_tmem = tmem + TM_S + sid * KH, do_tmem = tmem + TM_O + sid * HD;
+      auto issue_s = [&](int j) {  // S(j) of this stream: keys [64 hh, +64) of block j are rows 64 hh.. of the K tile
         const int s = j % NS;
         ptx::mbar_wait(&bars[B_KFULL + s], (j / NS) & 1);
-        const uint64_t dk = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_K + s * TILE_BYTES), 16, 1024);
-        for (int t = 0; t < ntiles; ++t) {
-          if (j > 0) ptx::mbar_wait(&bars[B_SFREE + t], (j - 1) & 1);  // softmax t holds S_t(j-1) in registers
-          ptx::tc_fence_after();
-          const uint64_t dq = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_Q + t * TILE_BYTES), 16, 1024);
+        if (j > 0) ptx::mbar_wait(&bars[B_SFREE + sid], (j - 1) & 1);  // the softmax warps hold S(j-1) in registers
+        ptx::tc_fence_after();
+        const uint64_t dk = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_K + s * TILE_BYTES + hh * (KH * 128)), 16, 1024);
 #pragma unroll
-          for (int k = 0; k < HD / 16; ++k)
-            ptx::mma_f16_ss(tmem + TM_S + t * BKV, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
-          ptx::tc_commit(&bars[B_SFULL + t]);
-        }
+        for (int k = 0; k < HD / 16; ++k) ptx::mma_f16_ss(ds_tmem, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+        ptx::tc_commit(&bars[B_SFULL + sid]);
         ptx::tc_commit(&bars[B_KEMPTY + s]);
       };
       ptx::mbar_wait(&bars[B_QFULL], 0);
@@ -145,46 +152,36 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         if (j + 1 < nblk) issue_s(j + 1);
         const int s = j % NS;
         ptx::mbar_wait(&bars[B_VFULL + s], (j / NS) & 1);
-        const uint32_t sv = ptx::smem_u32(smem + OFF_V + s * TILE_BYTES);
-        for (int t = 0; t < ntiles; ++t) {
-          ptx::mbar_wait(&bars[B_PFULL + t], j & 1);  // P_t(j) is in smem, PV_t(j-1) has been read out of TMEM
-          ptx::tc_fence_after();
-          const uint32_t sp = ptx::smem_u32(smem + OFF_P + t * 2 * TILE_BYTES);
+        ptx::mbar_wait(&bars[B_PFULL + sid], j & 1);  // P(j) is in smem, PV(j-1) has been read out of TMEM if rescaled
+        ptx::tc_fence_after();
+        const uint32_t sv = ptx::smem_u32(smem + OFF_V + s * TILE_BYTES) + hh * (KH * 128);
 #pragma unroll
-          for (int k = 0; k < BKV / 16; ++k) {
-            const uint64_t dp = ptx::make_sw128_desc(sp + (k >> 2) * TILE_BYTES, 16, 1024) + 2 * (k & 3);
-            const uint64_t dv = ptx::make_sw128_desc(sv + k * 2048, 1024, 1024);
-            ptx::mma_f16_ss(tmem + TM_O + t * HD, dp, dv, idesc_pv, (j | k) != 0);  // O accumulates in TMEM
-          }
-          ptx::tc_commit(&bars[B_PVDONE + t]);
+        for (int k = 0; k < KH / 16; ++k) {
+          const uint64_t dv = ptx::make_sw128_desc(sv + k * 2048, 1024, 1024);
+          ptx::mma_f16_ss(do_tmem, dp + 2 * k, dv, idesc_pv, (j | k) != 0);  // O accumulates in TMEM
         }
+        ptx::tc_commit(&bars[B_PVDONE + sid]);
         ptx::tc_commit(&bars[B_VEMPTY + s]);
       }
     }
   } else {
-    // ------------------------------------------------------------------ softmax groups
-    // 8 warps per tile: two warps share each TMEM lane quadrant (warp ids 4 apart) and split the 128 keys of a block,
-    // so a thread owns one query row x 64 keys.  Four warps per scheduler instead of two hide the MUFU / TMEM latencies.
-    const int sw = warp - 2;        // 0..15
-    const int t = sw >> 3;          // tile / group
+    // ------------------------------------------------------------------ softmax warps: stream (warp-5)/4, TMEM lane quadrant warp%4
+    const int sid = (warp - 5) >> 2, t = sid >> 1, hh = sid & 1;
     if (t < ntiles) {
-      const int q = warp & 3;       // TMEM lane quadrant of this warp
-      const int hc = (sw >> 2) & 1; // which 64 keys of the block
+      const int q = warp & 3;       // TMEM lane quadrant this warp may access
       const int r = q * 32 + lane;  // query row inside the tile == TMEM lane
       const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-      const uint32_t ts = trow + TM_S + t * BKV + hc * 64, to = trow + TM_O + t * HD + hc * 32;
+      const uint32_t ts = trow + TM_S + sid * KH, to = trow + TM_O + sid * HD;
       const float C2 = 0.125f * 1.4426950408889634f;  // scale * log2(e)
       float m = -INFINITY, l = 0.f;  // m: reference max (RAW, unscaled bf16 scores) of the exponentials; may be stale
-      uint8_t* prow = smem + OFF_P + (t * 2 + hc) * TILE_BYTES + r * 128;  // this thread's 64 keys = one swizzle atom row
-      float* xch = reinterpret_cast<float*>(smem + OFF_X);                 // [2 parities][2 tiles][2 halves][128 rows]
-      const int pair_bar = 1 + t * 4 + q;                                  // named barrier of the two partner warps
+      uint8_t* prow = smem + OFF_P + sid * TILE_BYTES + r * 128;  // this thread's 64 keys = one swizzle atom row
       for (int j = 0; j < nblk; ++j) {
-        ptx::mbar_wait(&bars[B_SFULL + t], j & 1);
+        ptx::mbar_wait(&bars[B_SFULL + sid], j & 1);
         ptx::tc_fence_after();
         // ---- 64 scores of the row -> registers, rounded to bf16 and packed
         uint32_t sp[32];
 #pragma unroll
-        for (int c0 = 0; c0 < 64; c0 += 32) {
+        for (int c0 = 0; c0 < KH; c0 += 32) {
           float sv[32];
           ptx::tmem_ld32(ts + c0, sv);
           ptx::tmem_ld_wait();
@@ -193,9 +190,9 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         }
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&bars[B_SFREE + t]);  // the next S MMA of this tile may start
-        const int kvalid = ntok - j * BKV - hc * 64;  // keys >= kvalid (in this thread's 64) are outside the frame
-        if (kvalid < 64) {
+        if (lane == 0) ptx::mbar_arrive(&bars[B_SFREE + sid]);  // the next S MMA of this stream may start
+        const int kvalid = ntok - j * BKV - hh * KH;  // keys >= kvalid (in this thread's 64) are outside the frame
+        if (kvalid < KH) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
             if (2 * i >= kvalid) sp[i] = 0xFF80FF80u;
@@ -209,18 +206,14 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
           mxb = bf16x2_max(mxb, sp[i + 1]);
         }
         mxa = bf16x2_max(mxa, mxb);
-        float bm = fmaxf(bf16lo_to_f32(mxa), bf16hi_to_f32(mxa));
-        // block max of the whole row: exchange with the partner warp (double-buffered by block parity: one barrier)
-        float* xm = xch + (((j & 1) * 2 + t) * 2) * 128;
-        xm[hc * 128 + r] = bm;
-        asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-        bm = fmaxf(bm, xm[(hc ^ 1) * 128 + r]);
+        const float bm = fmaxf(bf16lo_to_f32(mxa), bf16hi_to_f32(mxa));  // block max over this stream's 64 keys
         // Lazy rescale: the reference max only moves when the block max exceeds it by more than 2^8 in the exponent
         // (probabilities then stay <= 256, harmless in bf16 / fp32); O and l are rescaled only on those blocks.
-        const bool need = (bm - m) * C2 > 8.0f;  // always true on the first block (m = -inf); identical in both partners
+        // (bm = -inf when all 64 keys are outside the frame: nothing moves, every probability is 0.)
+        const bool need = bm > -INFINITY && (bm - m) * C2 > 8.0f;  // true on the first block with a key in the frame
         const float alpha = need ? ex2_approx((m - bm) * C2) : 1.0f;
         if (need) m = bm;
-        const float mb = m * C2;
+        const float mb = (m > -INFINITY) ? m * C2 : 0.f;
         // ---- probabilities -> bf16 (in place)
         float psum0 = 0.f, psum1 = 0.f;
 #pragma unroll
@@ -231,18 +224,21 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
           psum1 += p1;
           sp[i] = pack_bf16x2(p0, p1);
         }
-        l = fmaf(l, alpha, psum0 + psum1);  // partial row sum (this thread's keys); the halves are added at the end
-        // ---- PV_{j-1} must be complete before P (smem) is overwritten or O (TMEM) is rescaled
+        l = fmaf(l, alpha, psum0 + psum1);  // row sum over this stream's keys; the halves are merged at the end
+        // ---- PV(j-1) must be complete before P (smem) is overwritten or O (TMEM) is rescaled
         if (j > 0) {
-          ptx::mbar_wait(&bars[B_PVDONE + t], (j - 1) & 1);
+          ptx::mbar_wait(&bars[B_PVDONE + sid], (j - 1) & 1);
           ptx::tc_fence_after();
-          if (__any_sync(0xffffffffu, need)) {  // this thread rescales its 32 of the row's 64 output columns
-            float ov[32];
-            ptx::tmem_ld32(to, ov);
-            ptx::tmem_ld_wait();
+          if (__any_sync(0xffffffffu, need)) {
+#pragma unroll 1
+            for (int c0 = 0; c0 < HD; c0 += 32) {
+              float ov[32];
+              ptx::tmem_ld32(to + c0, ov);
+              ptx::tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) ov[i] *= alpha;
-            ptx::tmem_st32(to, ov);
+              for (int i = 0; i < 32; ++i) ov[i] *= alpha;
+              ptx::tmem_st32(to + c0, ov);
+            }
             ptx::tmem_st_wait();
           }
         }
@@ -253,26 +249,41 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         ptx::fence_proxy_async();  // generic-proxy P writes -> visible to the tensor core (async proxy)
         ptx::tc_fence_before();    // TMEM accesses of this iteration are complete
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&bars[B_PFULL + t]);
+        if (lane == 0) ptx::mbar_arrive(&bars[B_PFULL + sid]);
       }
-      ptx::mbar_wait(&bars[B_PVDONE + t], (nblk - 1) & 1);
+      ptx::mbar_wait(&bars[B_PVDONE + sid], (nblk - 1) & 1);
       ptx::tc_fence_after();
-      float oacc[32];  // this thread's 32 output columns
-      ptx::tmem_ld32(to, oacc);
-      ptx::tmem_ld_wait();
-      float* xs = xch + 4 * 2 * 128 + (t * 2) * 128;  // row sums of the two halves
-      xs[hc * 128 + r] = l;
-      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-      const float inv = 1.f / (l + xs[(hc ^ 1) * 128 + r]);
-      // ---- normalise, round, and store through this warp's (now idle) P rows: 32 rows x 64 B, row-contiguous stores
-      uint8_t* wst = smem + OFF_P + (t * 2 + hc) * TILE_BYTES + q * 32 * 128;  // written only by this warp's threads
+      // ---- merge the two key halves of the tile: exchange (m, l) with the partner stream's warp of the same quadrant;
+      // after the barrier the partner has seen its own last PV complete, so both O accumulators are final
+      float2* xs = reinterpret_cast<float2*>(smem + OFF_X) + (t * 2) * 128;
+      xs[hh * 128 + r] = make_float2(m, l);
+      ptx::tc_fence_before();
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + t * 4 + q) : "memory");
+      ptx::tc_fence_after();
+      const float2 pml = xs[(hh ^ 1) * 128 + r];
+      const float mm = fmaxf(m, pml.x);  // finite: block 0 of key half 0 always holds a key of the frame
+      const float a_own = ex2_approx((m - mm) * C2), a_par = ex2_approx((pml.x - mm) * C2);
+      const float inv = 1.f / fmaf(l, a_own, pml.y * a_par);
+      const float c_own = a_own * inv, c_par = a_par * inv;
+      // this warp writes output columns [32 hh, +32) of its 32 rows: own and partner accumulator, normalised
+      float oacc[32];
+      {
+        float opar[32];
+        ptx::tmem_ld32(to + hh * 32, oacc);
+        ptx::tmem_ld32(trow + TM_O + (sid ^ 1) * HD + hh * 32, opar);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) oacc[i] = fmaf(oacc[i], c_own, opar[i] * c_par);
+      }
+      // ---- round and store through this warp's (now idle) P rows: 32 rows x 64 B, row-contiguous stores
+      uint8_t* wst = smem + OFF_P + sid * TILE_BYTES + q * 32 * 128;  // written only by this warp's threads
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
         uint4 u;
-        u.x = pack_bf16x2(oacc[8 * g] * inv, oacc[8 * g + 1] * inv);
-        u.y = pack_bf16x2(oacc[8 * g + 2] * inv, oacc[8 * g + 3] * inv);
-        u.z = pack_bf16x2(oacc[8 * g + 4] * inv, oacc[8 * g + 5] * inv);
-        u.w = pack_bf16x2(oacc[8 * g + 6] * inv, oacc[8 * g + 7] * inv);
+        u.x = pack_bf16x2(oacc[8 * g], oacc[8 * g + 1]);
+        u.y = pack_bf16x2(oacc[8 * g + 2], oacc[8 * g + 3]);
+        u.z = pack_bf16x2(oacc[8 * g + 4], oacc[8 * g + 5]);
+        u.w = pack_bf16x2(oacc[8 * g + 6], oacc[8 * g + 7]);
         *reinterpret_cast<uint4*>(wst + lane * 64 + ((g ^ ((lane >> 1) & 3)) << 4)) = u;
       }
       __syncwarp();
@@ -282,7 +293,7 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         const int rr = 8 * it + (lane >> 2);
         const int qrow = q0 + t * BQ + q * 32 + rr;
         const uint4 u = *reinterpret_cast<const uint4*>(wst + rr * 64 + ((g ^ ((rr >> 1) & 3)) << 4));
-        if (qrow < ntok) *reinterpret_cast<uint4*>(o + ((long long)row0 + qrow) * D + h * HD + hc * 32 + 8 * g) = u;
+        if (qrow < ntok) *reinterpret_cast<uint4*>(o + ((long long)row0 + qrow) * D + h * HD + hh * 32 + 8 * g) = u;
       }
     }
     ptx::tc_fence_before();
