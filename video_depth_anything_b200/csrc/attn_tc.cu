@@ -26,6 +26,14 @@
 #include "ptx.cuh"
 #include "tmap.h"
 
+#ifdef FA_TRACE  // per-phase clock64 timeline of the four softmax warps of one scheduler (scripts/fa_trace.py); debugging aid
+__device__ long long g_fa_trace[4 * 16 * 8];  // [stream][block j][event]
+#define FA_T(ev) do { if (blockIdx.x == 2 && blockIdx.y == 5 && blockIdx.z == 7 && q == 2 && lane == 0 && j < 16) \
+                        g_fa_trace[(sid * 16 + j) * 8 + (ev)] = clock64(); } while (0)
+extern "C" int vda_debug_fa_trace(long long* out) { return (int)cudaMemcpyFromSymbol(out, g_fa_trace, sizeof(g_fa_trace)); }
+#else
+#define FA_T(ev)
+#endif
 namespace {
 
 constexpr int BQ = 128, BKV = 128, HD = 64, KH = 64;  // KH: keys per stream and block
@@ -175,9 +183,14 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
       const float C2 = 0.125f * 1.4426950408889634f;  // scale * log2(e)
       float m = -INFINITY, l = 0.f;  // m: reference max (RAW, unscaled bf16 scores) of the exponentials; may be stale
       uint8_t* prow = smem + OFF_P + sid * TILE_BYTES + r * 128;  // this thread's 64 keys = one swizzle atom row
+      // The barrier unit answers a phase test after ~200 clk even when the phase completed long ago, and this loop is a
+      // chain of dependent steps: the tests of "S(j+1) ready" and "PV(j-1) done" are issued early and consumed later.
+      uint32_t s_ok = 0;
       for (int j = 0; j < nblk; ++j) {
-        ptx::mbar_wait(&bars[B_SFULL + sid], j & 1);
+        FA_T(0);
+        if (!s_ok) ptx::mbar_wait(&bars[B_SFULL + sid], j & 1);
         ptx::tc_fence_after();
+        FA_T(1);
         // ---- 64 scores of the row -> registers, rounded to bf16 and packed
         uint32_t sp[32];
 #pragma unroll
@@ -191,6 +204,7 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&bars[B_SFREE + sid]);  // the next S MMA of this stream may start
+        FA_T(2);
         const int kvalid = ntok - j * BKV - hh * KH;  // keys >= kvalid (in this thread's 64) are outside the frame
         if (kvalid < KH) {
 #pragma unroll
@@ -214,6 +228,8 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         const float alpha = need ? ex2_approx((m - bm) * C2) : 1.0f;
         if (need) m = bm;
         const float mb = (m > -INFINITY) ? m * C2 : 0.f;
+        const uint32_t pv_ok = (j > 0) ? ptx::mbar_test(&bars[B_PVDONE + sid], (j - 1) & 1) : 1u;
+        FA_T(3);
         // ---- probabilities -> bf16 (in place)
         float psum0 = 0.f, psum1 = 0.f;
 #pragma unroll
@@ -225,9 +241,10 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
           sp[i] = pack_bf16x2(p0, p1);
         }
         l = fmaf(l, alpha, psum0 + psum1);  // row sum over this stream's keys; the halves are merged at the end
+        FA_T(4);
         // ---- PV(j-1) must be complete before P (smem) is overwritten or O (TMEM) is rescaled
         if (j > 0) {
-          ptx::mbar_wait(&bars[B_PVDONE + sid], (j - 1) & 1);
+          if (!pv_ok) ptx::mbar_wait(&bars[B_PVDONE + sid], (j - 1) & 1);
           ptx::tc_fence_after();
           if (__any_sync(0xffffffffu, need)) {
 #pragma unroll 1
@@ -242,6 +259,8 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
             ptx::tmem_st_wait();
           }
         }
+        FA_T(5);
+        s_ok = (j + 1 < nblk) ? ptx::mbar_test(&bars[B_SFULL + sid], (j + 1) & 1) : 0u;
         // ---- P -> swizzled smem (A operand of the PV MMA)
 #pragma unroll
         for (int g = 0; g < 8; ++g)
@@ -250,6 +269,7 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         ptx::tc_fence_before();    // TMEM accesses of this iteration are complete
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&bars[B_PFULL + sid]);
+        FA_T(6);
       }
       ptx::mbar_wait(&bars[B_PVDONE + sid], (nblk - 1) & 1);
       ptx::tc_fence_after();
