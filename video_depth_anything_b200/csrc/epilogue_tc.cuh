@@ -115,10 +115,14 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
       for (int i = 0; i < 32; i += 4) {
         const float4 b4 = *reinterpret_cast<const float4*>(bv + i), g4 = *reinterpret_cast<const float4*>(bv + 32 + i);
         const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, gb[4] = {g4.x, g4.y, g4.z, g4.w};
+        // roundings to bf16 go through the paired convert (one F2FP per two values) instead of one F2F each
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const float val = round_bf16(v[i + k] + bb[k]), gate = round_bf16(g[i + k] + gb[k]);
-          v[i + k] = val * round_bf16(gelu_fast(gate));
+        for (int k = 0; k < 4; k += 2) {
+          const uint32_t vr = pack_bf16x2(v[i + k] + bb[k], v[i + k + 1] + bb[k + 1]);
+          const uint32_t gr = pack_bf16x2(g[i + k] + gb[k], g[i + k + 1] + gb[k + 1]);
+          const uint32_t ar = pack_bf16x2(gelu_fast(bf16lo_to_f32(gr)), gelu_fast(bf16hi_to_f32(gr)));
+          v[i + k] = bf16lo_to_f32(vr) * bf16lo_to_f32(ar);
+          v[i + k + 1] = bf16hi_to_f32(vr) * bf16hi_to_f32(ar);
         }
       }
     } else {
@@ -133,7 +137,11 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
       // the activation switch stays outside the element loops: one compact loop runs, the others are never fetched
       if (act == VDA_ACT_GELU) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gelu_fast(round_bf16(v[i]));
+        for (int i = 0; i < 32; i += 2) {  // fc1's output is a bf16 tensor: round (paired convert), then GELU
+          const uint32_t r = pack_bf16x2(v[i], v[i + 1]);
+          v[i] = gelu_fast(bf16lo_to_f32(r));
+          v[i + 1] = gelu_fast(bf16hi_to_f32(r));
+        }
       } else if (act == VDA_ACT_RELU) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
