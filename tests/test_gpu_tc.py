@@ -75,7 +75,8 @@ def test_gemm_tc_epilogues():
     bf16_close("tc_convt", _unpad(out, Bf, H * k, W_ * k).float(), ref)
 
 
-@pytest.mark.parametrize("Ci,Co,H,W", [(64, 64, 12, 10), (48, 64, 20, 17), (256, 128, 30, 30), (1024, 256, 19, 19)])
+@pytest.mark.parametrize("Ci,Co,H,W", [(64, 64, 12, 10), (48, 64, 20, 17), (256, 128, 30, 30), (1024, 256, 19, 19),
+                                        (256, 128, 61, 57), (128, 96, 70, 45)])
 def test_conv3x3_tc(Ci, Co, H, W):
     from video_depth_anything_b200.engine import _conv3x3_pack
     L, lib = _lib()

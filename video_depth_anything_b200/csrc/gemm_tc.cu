@@ -241,15 +241,23 @@ int launch_kind(const vda_gemm_desc* d, cudaStream_t st) {
 
 }  // namespace
 
-int vda_gemm_tc_pair(const vda_gemm_desc* d, cudaStream_t st);  // gemm_tc2.cu
+int vda_gemm_tc_pair(const vda_gemm_desc* d, cudaStream_t st);       // gemm_tc2.cu
+int vda_conv3x3_tc_shared(const vda_gemm_desc* d, cudaStream_t st);  // conv_tc.cu
 
-// VDA_NO_PAIR=1 keeps every GEMM on the single-CTA kernel (A/B measurements).
+// VDA_NO_PAIR=1 keeps every GEMM on the single-CTA kernel, VDA_NO_CONVSHARE=1 keeps the narrow 3x3 convolutions on the
+// per-tap kernel (A/B measurements).
+static bool env_off(const char* name) {
+  const char* s = getenv(name);
+  return s && s[0] == '1';
+}
 static bool pair_enabled() {
   static int v = -1;
-  if (v < 0) {
-    const char* s = getenv("VDA_NO_PAIR");
-    v = (s && s[0] == '1') ? 0 : 1;
-  }
+  if (v < 0) v = env_off("VDA_NO_PAIR") ? 0 : 1;
+  return v == 1;
+}
+static bool convshare_enabled() {
+  static int v = -1;
+  if (v < 0) v = env_off("VDA_NO_CONVSHARE") ? 0 : 1;
   return v == 1;
 }
 
@@ -268,6 +276,10 @@ int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
     VDA_CHECK_ARG(d->N <= 32, "vda_gemm(tc, tf32): only the N <= 32 output head is instantiated");
     return launch_tc<32, bf16, true, true>(d, st);
   }
+  // 3x3 convolutions: tap-sharing kernel (one A load per three taps, two M tiles per weight tile)
+  if (d->taps == 9 && d->ksplit == 1 && d->N > 64 && d->K % 64 == 0 && d->head_w == nullptr &&
+      d->M >= 2048 && convshare_enabled())
+    return vda_conv3x3_tc_shared(d, st);
   int bn;
   if (d->N <= 32) bn = 32;
   else if (d->N <= 64) bn = 64;
