@@ -12,7 +12,8 @@ dev = "cuda"
 L.require_device(dev)
 lib = L.load()
 M = 43840
-shapes = [("qkv", 3072, 1024, "store"), ("proj", 1024, 1024, "resid"), ("fc1", 4096, 1024, "gelu"), ("fc2", 1024, 4096, "resid")]
+shapes = [("qkv", 3072, 1024, "store"), ("proj", 1024, 1024, "resid"), ("fc1", 4096, 1024, "gelu"), ("fc2", 1024, 4096, "resid"),
+          ("projS", 1024, 1024, "store"), ("fc2S", 1024, 4096, "store")]
 if len(sys.argv) > 1:
     shapes = [s for s in shapes if s[0] in sys.argv[1:]]
 for name, N, K, kind in shapes:

@@ -158,6 +158,32 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
   }
   __syncwarp();
   // ---------------------------------------------------------------- phase 2
+  if constexpr (EK == EK_RESID) {
+    // resid += gamma * v as fire-and-forget vector reductions (the L2 performs the single fp32 add: the same bits as
+    // load-add-store, denormals aside: REDG flushes them).  A lane takes FOUR columns, so the sixteen lanes of a row
+    // cover its 256 B contiguously and every 32 B sector is reduced by one request: with eight columns per lane and two
+    // reductions each, every sector was hit twice, the L2 reduction rate (not HBM) bounded the kernel and `proj`
+    // (K = 1024) could not hide it (123 us against 79 us with a plain store; 104 us now).  A prefetched
+    // load - add - store of the same tile was slower still (136 us).
+    const int cj = lane & 15;
+    const int col4 = n0 + c + 4 * cj;
+    const float4 g4 = *reinterpret_cast<const float4*>(e.gamma + col4);
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+      const int rr = 2 * t + (lane >> 4);
+      const uint2 p = *reinterpret_cast<const uint2*>(stage + rr * 128 + (((cj >> 1) ^ (rr & 7)) << 4) + ((cj & 1) << 3));
+      const int orow = __shfl_sync(0xffffffffu, ri.out_row, rr);
+      const int drow = __shfl_sync(0xffffffffu, ri.resid_row, rr);
+      if (orow < 0) continue;
+      float* rp = e.resid + (long long)drow * e.ldresid + col4;
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(rp), "f"(__fmul_rn(bf16lo_to_f32(p.x), g4.x)),
+                   "f"(__fmul_rn(bf16hi_to_f32(p.x), g4.y)), "f"(__fmul_rn(bf16lo_to_f32(p.y), g4.z)),
+                   "f"(__fmul_rn(bf16hi_to_f32(p.y), g4.w))
+                   : "memory");
+    }
+    __syncwarp();  // the tile is rewritten by the next chunk
+    return;
+  }
   float gam[8];
   if (has_resid && !assign) {
     const float4 g0 = *reinterpret_cast<const float4*>(e.gamma + col), g1 = *reinterpret_cast<const float4*>(e.gamma + col + 4);
