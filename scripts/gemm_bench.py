@@ -13,7 +13,8 @@ L.require_device(dev)
 lib = L.load()
 M = 43840
 shapes = [("qkv", 3072, 1024, "store"), ("proj", 1024, 1024, "resid"), ("fc1", 4096, 1024, "gelu"), ("fc2", 1024, 4096, "resid"),
-          ("projS", 1024, 1024, "store"), ("fc2S", 1024, 4096, "store")]
+          ("projS", 1024, 1024, "store"), ("fc2S", 1024, 4096, "store"), ("projRelu", 1024, 1024, "relu2"),
+          ("projRes", 1024, 1024, "res"), ("projResIn", 1024, 1024, "resin"), ("mmRes", 256, 256, "res"), ("mmS", 256, 256, "store")]
 if len(sys.argv) > 1:
     shapes = [s for s in shapes if s[0] in sys.argv[1:]]
 for name, N, K, kind in shapes:
@@ -37,6 +38,14 @@ for name, N, K, kind in shapes:
         d.out, d.ldo = out.data_ptr(), N
         d.act = L.ACT_GELU if kind == "gelu" else L.ACT_NONE
         keep.append(out)
+        if kind == "relu2":
+            o2 = torch.empty_like(out)
+            d.out_relu = o2.data_ptr()
+            keep.append(o2)
+        if kind in ("res", "resin"):
+            r = out if kind == "resin" else torch.randn(M, N, device=dev).bfloat16()
+            d.res, d.ldres = r.data_ptr(), N
+            keep.append(r)
     for _ in range(3):
         L.gemm(d)
     torch.cuda.synchronize()

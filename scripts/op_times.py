@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--size", type=int, default=518)
     ap.add_argument("--repeats", type=int, default=7)
     ap.add_argument("--out", default="gpurun_out/op_times.json")
+    ap.add_argument("--in-situ", action="store_true", help="time the ops inside back-to-back steps (events between ops, no flush)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     torch.manual_seed(0)
@@ -36,9 +37,24 @@ def main():
     torch.cuda.synchronize()
     rows = []
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    situ = None
+    if a.in_situ:
+        n = len(plan.ops)
+        acc = [[] for _ in range(n)]
+        for _ in range(a.repeats):
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(n + 1)]
+            evs[0].record()
+            for idx, (fn, args) in enumerate(plan.ops):
+                rc = fn(C.byref(args[0]), st) if fn is lib.vda_gemm else fn(*args, st)
+                L.check(rc, "op %d" % idx)
+                evs[idx + 1].record()
+            torch.cuda.synchronize()
+            for idx in range(n):
+                acc[idx].append(evs[idx].elapsed_time(evs[idx + 1]) * 1e3)
+        situ = [sorted(x)[len(x) // 2] for x in acc]
     for idx, (fn, args) in enumerate(plan.ops):
         ts = []
-        for _ in range(a.repeats):
+        for _ in range(0 if situ else a.repeats):
             flush.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -48,7 +64,7 @@ def main():
             torch.cuda.synchronize()
             ts.append(e0.elapsed_time(e1) * 1e3)
         ts.sort()
-        us = ts[len(ts) // 2]
+        us = situ[idx] if situ else ts[len(ts) // 2]
         if fn is lib.vda_gemm:
             d = args[0]
             fl = 2.0 * d.M * d.N * d.K * d.taps * d.ksplit
@@ -65,7 +81,7 @@ def main():
         g["fl"] += r.get("flops", 0.0)
         g["n"] += 1
         g["us"] += r["us"]
-    print(f"{len(rows)} ops, {total / 1e3:.2f} ms summed (L2 flushed before each op)")
+    print(f"{len(rows)} ops, {total / 1e3:.2f} ms summed ({'in situ: events between the ops of back-to-back steps' if situ else 'L2 flushed before each op'})")
     for key, g in sorted(agg.items(), key=lambda kv: -kv[1]["us"]):
         op, M, N, K, taps, act, mp = key
         shape = f"M={M} N={N} K={K} taps={taps} act={act} map={mp}" if op == "gemm" else ""

@@ -226,6 +226,8 @@ int launch_conv(const vda_gemm_desc* d, cudaStream_t st) {
 
 // taps == 9, ksplit == 1, bf16 x bf16, N > 64, K % 64 == 0: checked by the caller (vda_gemm_tc).
 int vda_conv3x3_tc_shared(const vda_gemm_desc* d, cudaStream_t st) {
-  if (epi_kind_of(d) == EK_STORE) return launch_conv<EK_STORE>(d, st);
+  const int kind = epi_kind_of(d);
+  if (kind == EK_STORE) return launch_conv<EK_STORE>(d, st);
+  if (kind == EK_RES) return launch_conv<EK_RES>(d, st);
   return launch_conv<EK_GENERIC>(d, st);
 }

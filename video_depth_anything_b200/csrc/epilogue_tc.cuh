@@ -19,7 +19,8 @@ enum EpiKind {
   EK_GELU = 1,     // out = R(gelu(R(acc + bias)))                         (mlp.fc1)
   EK_RESID = 2,    // resid += gamma * R(acc + bias), nothing else stored  (attn.proj, mlp.fc2)
   EK_GEGLU = 3,    // out = R(value * R(gelu(gate)))                       (motion-module feed-forward)
-  EK_GENERIC = 4   // everything, decided at run time
+  EK_GENERIC = 4,  // everything, decided at run time
+  EK_RES = 5       // out = R(R(acc + bias) + res)                         (motion-module out / ff / proj_out skips)
 };
 
 static inline int epi_kind_of(const vda_gemm_desc* d) {
@@ -30,6 +31,9 @@ static inline int epi_kind_of(const vda_gemm_desc* d) {
     if (d->act == VDA_ACT_GEGLU) return EK_GEGLU;
   }
   if (plain && d->resid != nullptr && !d->resid_assign && d->out == nullptr && d->act == VDA_ACT_NONE) return EK_RESID;
+  if (d->res != nullptr && d->res2 == nullptr && d->out_relu == nullptr && d->head_w == nullptr && d->resid == nullptr &&
+      d->out != nullptr && d->act == VDA_ACT_NONE && d->out_map != VDA_MAP_CONVT)
+    return EK_RES;
   return EK_GENERIC;
 }
 
@@ -61,12 +65,19 @@ __device__ __forceinline__ bool epi_fast_ok(const Epi& e, int n) {
   return true;
 }
 
+__device__ __forceinline__ uint32_t relu_bf16x2(uint32_t a) {
+  uint32_t r;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(0u));
+  return r;
+}
+
 // stage: this warp's 4 KB tile (1024B aligned); sbias: bias values of the CTA tile's accumulator columns, indexed by
 // the tile-local accumulator column; tcol: TMEM address of (this warp's lane quadrant, tile-local accumulator column c).
 template <int EK, bool GEGLU>
 __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int n0, int c, uint32_t tcol, uint8_t* stage,
                                              const float* sbias, int lane) {
   static_assert((EK == EK_GEGLU) == GEGLU || EK == EK_GENERIC, "GEGLU flag must match the kind");
+  constexpr bool RESK = EK == EK_RES;
   constexpr bool GEN = EK == EK_GENERIC;
   const int act = GEN ? e.act : (EK == EK_GELU ? (int)VDA_ACT_GELU : (int)VDA_ACT_NONE);
   const bool has_resid = GEN ? (e.resid != nullptr) : (EK == EK_RESID);
@@ -86,19 +97,18 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
     ocol = col - kk * e.ct_cout;
     row_add = (kk / e.ct_k) * (e.gw * e.ct_k + 2) + (kk % e.ct_k);
   }
-  // skip connections: fetch this lane's phase-2 operands now, so that their latency hides behind phase 1
-  uint4 rv[(GEN && !GEGLU) ? 8 : 1], rv2[(GEN && !GEGLU) ? 8 : 1];
-  if constexpr (GEN && !GEGLU) {
-    if (has_res) {
+  // EK_RES: the skip operand in phase-2 coordinates (8 lanes cover the 128 B of a row segment), requested before the
+  // accumulator read so the round trip hides behind phase 1.  Only this lean kind does it: with the run-time flags of
+  // the generic kind in the same function ptxas spilled the prefetched values, which serialised the loads.
+  uint4 rv[RESK ? 8 : 1];
+  if constexpr (RESK) {
 #pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        const int rr = 4 * t + (lane >> 3);
-        const int orow = __shfl_sync(0xffffffffu, ri.out_row, rr);
-        const int rrow = __shfl_sync(0xffffffffu, ri.res_row, rr);
-        rv[t] = make_uint4(0, 0, 0, 0);
-        if (orow >= 0)
-          rv[t] = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.res) + (long long)rrow * e.ldres + ocol);
-      }
+    for (int t = 0; t < 8; ++t) {
+      const int rr = 4 * t + (lane >> 3);
+      const int orow = __shfl_sync(0xffffffffu, ri.out_row, rr);
+      const int rrow = __shfl_sync(0xffffffffu, ri.res_row, rr);
+      rv[t] = make_uint4(0, 0, 0, 0);
+      if (orow >= 0) rv[t] = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.res) + (long long)rrow * e.ldres + col);
     }
   }
   // ---------------------------------------------------------------- phase 1
@@ -127,6 +137,23 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
       }
     } else {
       ptx::tmem_ld32(tcol + h * 32, v);
+      // Skip connections (GENERIC kind): this lane's row, the 32 columns of this half = 64 contiguous bytes = two full
+      // sectors per lane, requested before the accumulator wait so the latency hides behind it.  (Fetching them
+      // row-contiguously for phase 2 instead needed 32-64 more live registers: ptxas spilled the prefetched values,
+      // which serialised the loads -- the motion-module out-projections ran at 200 us against 85 us for a plain store.)
+      uint4 r1[(GEN && !GEGLU) ? 4 : 1], r2[(GEN && !GEGLU) ? 4 : 1];
+      if constexpr (GEN && !GEGLU) {
+        if (has_res && ri.out_row >= 0) {
+          const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.res) + (long long)ri.res_row * e.ldres + n0 + c + h * 32);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) r1[k] = rp[k];
+        }
+        if (has_res2 && ri.out_row >= 0) {
+          const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.res2) + (long long)ri.res_row * e.ldres + n0 + c + h * 32);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) r2[k] = rp[k];
+        }
+      }
       ptx::tmem_ld_wait();
       const float* bv = sbias + c + h * 32;
 #pragma unroll
@@ -145,6 +172,20 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
       } else if (act == VDA_ACT_RELU) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+      }
+      if constexpr (GEN && !GEGLU) {
+        if (has_res || has_res2) {  // R(R(R(conv) + x) + x2): every bf16 add of the reference rounds (blocks.py:91,155)
+          const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1);
+          const uint32_t* w2 = reinterpret_cast<const uint32_t*>(r2);
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            uint32_t u = pack_bf16x2(v[i], v[i + 1]);
+            if (has_res) u = pack_bf16x2(bf16lo_to_f32(u) + bf16lo_to_f32(w1[i >> 1]), bf16hi_to_f32(u) + bf16hi_to_f32(w1[i >> 1]));
+            if (has_res2) u = pack_bf16x2(bf16lo_to_f32(u) + bf16lo_to_f32(w2[i >> 1]), bf16hi_to_f32(u) + bf16hi_to_f32(w2[i >> 1]));
+            pk[h * 16 + (i >> 1)] = u;
+          }
+          continue;
+        }
       }
     }
 #pragma unroll
@@ -189,29 +230,32 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
     const float4 g0 = *reinterpret_cast<const float4*>(e.gamma + col), g1 = *reinterpret_cast<const float4*>(e.gamma + col + 4);
     gam[0] = g0.x; gam[1] = g0.y; gam[2] = g0.z; gam[3] = g0.w; gam[4] = g1.x; gam[5] = g1.y; gam[6] = g1.z; gam[7] = g1.w;
   }
-  if constexpr (GEN && !GEGLU) {
-    if (has_res2) {  // second skip connection: all eight loads in flight before the first use (pk[] is dead by now)
-#pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        const int rr = 4 * t + (lane >> 3);
-        const int orow = __shfl_sync(0xffffffffu, ri.out_row, rr);
-        const int rrow = __shfl_sync(0xffffffffu, ri.res_row, rr);
-        rv2[t] = make_uint4(0, 0, 0, 0);
-        if (orow >= 0)
-          rv2[t] = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.res2) + (long long)rrow * e.ldres + ocol);
-      }
-    }
-  }
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     const int rr = 4 * t + (lane >> 3);
     const uint4 p = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((j ^ (rr & 7)) << 4));
     const int orow = __shfl_sync(0xffffffffu, ri.out_row, rr);
-    const int rrow = __shfl_sync(0xffffffffu, ri.res_row, rr);
     const int drow = __shfl_sync(0xffffffffu, ri.resid_row, rr);
     if (orow < 0) continue;
+    if constexpr (RESK) {  // bf16 add of the reference: R(R(acc + bias) + skip)
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(&rv[t]);
+      const uint32_t* q = reinterpret_cast<const uint32_t*>(&p);
+      uint4 o;
+      uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        ow[k] = pack_bf16x2(bf16lo_to_f32(q[k]) + bf16lo_to_f32(w[k]), bf16hi_to_f32(q[k]) + bf16hi_to_f32(w[k]));
+      *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out) + (long long)(orow + row_add) * e.ldo + ocol) = o;
+      continue;
+    }
     if constexpr (EK == EK_STORE || EK == EK_GELU || EK == EK_GEGLU) {  // nothing to add: the staged bf16 is the output
       *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out) + (long long)(orow + row_add) * e.ldo + ocol) = p;
+      continue;
+    }
+    if (!has_resid) {  // skip connections were added in phase 1: the staged bf16 is the output (+ its ReLU copy)
+      const long long oo = (long long)(orow + row_add) * e.ldo + ocol;
+      *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out) + oo) = p;
+      if (has_relu) *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out_relu) + oo) = make_uint4(relu_bf16x2(p.x), relu_bf16x2(p.y), relu_bf16x2(p.z), relu_bf16x2(p.w));
       continue;
     }
     float v[8] = {bf16lo_to_f32(p.x), bf16hi_to_f32(p.x), bf16lo_to_f32(p.y), bf16hi_to_f32(p.y),
@@ -239,24 +283,6 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
         *reinterpret_cast<float4*>(rp + 4) = x1;
       }
       if (!has_out) continue;
-    }
-    if constexpr (GEN && !GEGLU) {
-      if (has_res) {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(&rv[t]);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          v[2 * k] = round_bf16(v[2 * k] + bf16lo_to_f32(w[k]));
-          v[2 * k + 1] = round_bf16(v[2 * k + 1] + bf16hi_to_f32(w[k]));
-        }
-      }
-      if (has_res2) {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(&rv2[t]);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          v[2 * k] = round_bf16(v[2 * k] + bf16lo_to_f32(w[k]));
-          v[2 * k + 1] = round_bf16(v[2 * k + 1] + bf16hi_to_f32(w[k]));
-        }
-      }
     }
     const long long oo = (long long)(orow + row_add) * e.ldo + ocol;
     Vec8<bf16>::store(reinterpret_cast<bf16*>(e.out) + oo, v);

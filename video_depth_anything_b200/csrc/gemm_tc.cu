@@ -235,6 +235,7 @@ int launch_kind(const vda_gemm_desc* d, cudaStream_t st) {
     case EK_GELU: return launch_tc<BN, bf16, true, false, EK_GELU>(d, st);
     case EK_RESID: return launch_tc<BN, bf16, true, false, EK_RESID>(d, st);
     case EK_GEGLU: return launch_tc<BN, bf16, true, false, EK_GEGLU>(d, st);
+    case EK_RES: return launch_tc<BN, bf16, true, false, EK_RES>(d, st);
     default: return launch_tc<BN, bf16, true, false, EK_GENERIC>(d, st);
   }
 }

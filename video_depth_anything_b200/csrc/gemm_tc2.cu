@@ -240,6 +240,7 @@ int vda_gemm_tc_pair(const vda_gemm_desc* d, cudaStream_t st) {
     case EK_GELU: return launch_tc2<EK_GELU>(d, st);
     case EK_RESID: return launch_tc2<EK_RESID>(d, st);
     case EK_GEGLU: return launch_tc2<EK_GEGLU>(d, st);
+    case EK_RES: return launch_tc2<EK_RES>(d, st);
     default: return launch_tc2<EK_GENERIC>(d, st);
   }
 }
