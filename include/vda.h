@@ -124,7 +124,8 @@ int vda_layernorm(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, cons
                   const float* pe, int32_t pe_group, int32_t pe_T, vda_stream_t stream);
 
 /* GroupNorm(groups, C, eps) per frame over dense tokens x[frames, hw, C] (motion_module.py:89,116) -> y tokens.
- * stats: scratch of frames*groups*2*33 doubles (mean/rstd + per-block partial sums; reduction is deterministic). */
+ * stats: scratch of frames*groups*2*34 doubles (mean/rstd, per-block partial sums, float copies for the apply pass;
+ *        the reduction is deterministic). */
 int vda_groupnorm_tokens(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, const float* w, const float* b,
                          float eps, int32_t frames, int32_t hw, int32_t C, int32_t groups, double* stats,
                          vda_stream_t stream);

@@ -188,7 +188,7 @@ def test_layernorm_groupnorm(mode):
         x = (torch.randn(frames, hw, C_, device=dev) * 1.5 + 0.3).to(dt)
         w, b = torch.rand(C_, device=dev) + 0.5, torch.randn(C_, device=dev)
         y = torch.zeros_like(x)
-        stt = torch.zeros(frames * 32 * 2 * 33, dtype=torch.float64, device=dev)
+        stt = torch.zeros(frames * 32 * 2 * 34, dtype=torch.float64, device=dev)
         L.check(lib.vda_groupnorm_tokens(x.data_ptr(), L.dt(x), y.data_ptr(), L.dt(y), w.data_ptr(), b.data_ptr(), 1e-6, frames, hw,
                                          C_, 32, stt.data_ptr(), st), "gn")
         ref = F.group_norm(x.float().permute(0, 2, 1), 32, w, b, 1e-6).permute(0, 2, 1)

@@ -113,9 +113,23 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(const TI* __restrict__ x,
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(hw, r0 + rows_per_block);
   if (rsub < rstep) {
-    for (int r = r0 + rsub; r < r1; r += rstep) {
+    const TI* xp = x + (long long)f * hw * C + cv * 8;
+    int r = r0 + rsub;
+    for (; r + 3 * rstep < r1; r += 4 * rstep) {  // four independent 16 B loads in flight per thread
+      float v[4][8];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) Vec8<TI>::load(xp + (long long)(r + u * rstep) * C, v[u]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          s[i] += v[u][i];
+          q[i] = fmaf(v[u][i], v[u][i], q[i]);
+        }
+    }
+    for (; r < r1; r += rstep) {
       float v[8];
-      Vec8<TI>::load(x + ((long long)f * hw + r) * C + cv * 8, v);
+      Vec8<TI>::load(xp + (long long)r * C, v);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         s[i] += v[i];
@@ -152,8 +166,8 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(const TI* __restrict__ x,
   }
 }
 
-__global__ void gn_finalize_kernel(const double* __restrict__ partial, double* __restrict__ stats, int nblocks, int groups,
-                                   double cnt, float eps, int total) {
+__global__ void gn_finalize_kernel(const double* __restrict__ partial, double* __restrict__ stats, float2* __restrict__ fstats,
+                                   int nblocks, int groups, double cnt, float eps, int total) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;  // (frame, group)
   if (i >= total) return;
   const int f = i / groups, g = i % groups;
@@ -168,12 +182,13 @@ __global__ void gn_finalize_kernel(const double* __restrict__ partial, double* _
   if (var < 0) var = 0;
   stats[2 * i] = mean;
   stats[2 * i + 1] = (double)rsqrtf((float)var + eps);
+  fstats[i] = make_float2((float)mean, rsqrtf((float)var + eps));  // what the apply pass reads (no fp64 there)
 }
 
 // y = a*x + b' with a = rstd*w, b' = -a*mean + bias (the fused-parameter form ATen uses).
 template <typename TI, typename TO, bool RB>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const TI* __restrict__ x, TO* __restrict__ y,
-                                                      const double* __restrict__ stats, const float* __restrict__ w,
+                                                      const float2* __restrict__ fstats, const float* __restrict__ w,
                                                       const float* __restrict__ b, int hw, int C, int groups,
                                                       long long total_vec) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -183,16 +198,24 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const TI* __restrict__ x,
   const long long row = idx / nv;
   const int f = (int)(row / hw);
   const int cpg = C / groups;
-  float v[8], o[8];
+  float v[8], o[8], wv[8], bv[8];
   Vec8<TI>::load(x + row * C + cv * 8, v);
+  Vec8<float>::load(w + cv * 8, wv);
+  Vec8<float>::load(b + cv * 8, bv);
+  if ((cpg & 7) == 0) {  // the 8 channels of this vector share a group
+    const float2 ms = fstats[(long long)f * groups + (cv * 8) / cpg];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    int ch = cv * 8 + i, g = ch / cpg;
-    const float mean = (float)stats[((long long)f * groups + g) * 2];
-    const float rstd = (float)stats[((long long)f * groups + g) * 2 + 1];
-    float a = rstd * w[ch];
-    float bb = -a * mean + b[ch];
-    o[i] = R<RB>(a * v[i] + bb);
+    for (int i = 0; i < 8; ++i) {
+      const float a = ms.y * wv[i];
+      o[i] = R<RB>(a * v[i] + (-a * ms.x + bv[i]));
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float2 ms = fstats[(long long)f * groups + (cv * 8 + i) / cpg];
+      const float a = ms.y * wv[i];
+      o[i] = R<RB>(a * v[i] + (-a * ms.x + bv[i]));
+    }
   }
   Vec8<TO>::store(y + row * C + cv * 8, o);
 }
@@ -227,24 +250,27 @@ extern "C" int vda_groupnorm_tokens(const void* x, int32_t x_dtype, void* y, int
                 C, groups);
   VDA_CHECK_ARG(x_dtype == y_dtype, "vda_groupnorm_tokens: x/y dtypes must match");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  int blocks_per_frame = (hw + 255) / 256;
+  int blocks_per_frame = (hw + 31) / 32;  // enough blocks to fill the machine: 32 frames x up to 32 blocks
   if (blocks_per_frame > GN_MAX_BLOCKS) blocks_per_frame = GN_MAX_BLOCKS;
   const int rpb = (hw + blocks_per_frame - 1) / blocks_per_frame;
   blocks_per_frame = (hw + rpb - 1) / rpb;
   dim3 g1(blocks_per_frame, frames);
   double* partial = stats + (size_t)frames * groups * 2;  // [frames][GN_MAX_BLOCKS][groups][2]
+  // float (mean, rstd) pairs for the apply pass (no fp64 conversions there) follow the partial sums: the caller sizes
+  // `stats` as frames * groups * 2 * (GN_MAX_BLOCKS + 2) doubles (include/vda.h).
+  float2* fstats = reinterpret_cast<float2*>(stats + (size_t)frames * groups * 2 * (GN_MAX_BLOCKS + 1));
   const long long total_vec = (long long)frames * hw * (C / 8);
   const unsigned g2 = (unsigned)((total_vec + 255) / 256);
   const double cnt = (double)hw * (C / groups);
   const int fg = frames * groups;
   if (x_dtype == VDA_BF16) {
     gn_stats_kernel<bf16><<<g1, 256, 0, st>>>((const bf16*)x, partial, hw, C, groups, rpb);
-    gn_finalize_kernel<<<(fg + 127) / 128, 128, 0, st>>>(partial, stats, blocks_per_frame, groups, cnt, eps, fg);
-    gn_apply_kernel<bf16, bf16, true><<<g2, 256, 0, st>>>((const bf16*)x, (bf16*)y, stats, w, b, hw, C, groups, total_vec);
+    gn_finalize_kernel<<<(fg + 127) / 128, 128, 0, st>>>(partial, stats, fstats, blocks_per_frame, groups, cnt, eps, fg);
+    gn_apply_kernel<bf16, bf16, true><<<g2, 256, 0, st>>>((const bf16*)x, (bf16*)y, fstats, w, b, hw, C, groups, total_vec);
   } else {
     gn_stats_kernel<float><<<g1, 256, 0, st>>>((const float*)x, partial, hw, C, groups, rpb);
-    gn_finalize_kernel<<<(fg + 127) / 128, 128, 0, st>>>(partial, stats, blocks_per_frame, groups, cnt, eps, fg);
-    gn_apply_kernel<float, float, false><<<g2, 256, 0, st>>>((const float*)x, (float*)y, stats, w, b, hw, C, groups, total_vec);
+    gn_finalize_kernel<<<(fg + 127) / 128, 128, 0, st>>>(partial, stats, fstats, blocks_per_frame, groups, cnt, eps, fg);
+    gn_apply_kernel<float, float, false><<<g2, 256, 0, st>>>((const float*)x, (float*)y, fstats, w, b, hw, C, groups, total_vec);
   }
   VDA_CUDA_LAUNCH_CHECK("groupnorm kernels");
   return 0;

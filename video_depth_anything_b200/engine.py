@@ -302,7 +302,7 @@ class ForwardPlan:
         qkv = self.buf(n + ".qkv", M, 3 * C)
         att = self.buf(n + ".att", M, C)
         ff = self.buf(n + ".ff", M, 4 * C)
-        stats = torch.empty((self.BT * 32 * 2 * 33,), dtype=torch.float64, device=self.device)
+        stats = torch.empty((self.BT * 32 * 2 * 34,), dtype=torch.float64, device=self.device)
         self.bufs[n + ".stats"] = stats
         self.op(lib.vda_groupnorm_tokens, x.data_ptr(), self.dcode, g.data_ptr(), self.dcode, W_[n + ".gn.w"].data_ptr(),
                 W_[n + ".gn.b"].data_ptr(), 1e-6, self.BT, hw, C, 32, stats.data_ptr(), launches=3)
