@@ -205,7 +205,8 @@ def test_bilinear_im2col_misc(mode):
     st = L.stream_ptr()
     dt = torch.bfloat16 if mode == "bf16" else torch.float32
     Bf, Cc = 2, 32
-    for (ih, iw, oh, ow) in ((5, 7, 10, 14), (9, 9, 19, 17), (12, 16, 21, 28)):
+    # the last three sizes take the shared-memory row kernel in bf16 (ow >= 32): 2x, a non-integer ratio, a ragged last tile
+    for (ih, iw, oh, ow) in ((5, 7, 10, 14), (9, 9, 19, 17), (12, 16, 21, 28), (19, 19, 37, 37), (37, 40, 74, 80), (20, 50, 33, 71)):
         x = torch.randn(Bf, Cc, ih, iw, device=dev).to(dt)
         xin = _pad_nhwc(x)
         out = torch.zeros(Bf * oh * ow, Cc, device=dev, dtype=dt)
