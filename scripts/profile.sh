@@ -10,7 +10,7 @@ cat gpurun_out/bench_$TAG.json | cut -c1-600
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 550 -c 600 --csv \
   --log-file gpurun_out/launches_$TAG.csv python bench.py $ARGS > gpurun_out/ncu_launches_$TAG.log 2>&1
 echo "launch list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_tc2_kernel --launch-skip 1 --launch-count 5 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_tc2_kernel --launch-skip 1 --launch-count 4 \
   -o gpurun_out/gemm_$TAG -f python bench.py $ARGS > gpurun_out/ncu_gemm_$TAG.log 2>&1
 echo "gemm full rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:flash_attn_tc_kernel --launch-skip 1 --launch-count 1 \
