@@ -142,6 +142,22 @@ def test_forward_contract():
         m(torch.zeros(1, 2, 3, 28, 28))  # CPU tensors are refused: there is no fallback path
 
 
+def test_graph_replay_matches_launch_loop():
+    """The plan captures its launch list into a CUDA graph after two eager runs: replays must reproduce the eager
+    result bit for bit (fp32 and bf16 builds), on fresh inputs too."""
+    m, sd = get_model("vits")
+    xa, xb = synthetic_clip(1, 4, 42, 56, 21).to(dev), synthetic_clip(1, 4, 42, 56, 22).to(dev)
+    for bf16 in (False, True):
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=bf16):
+            plan = m.plan(1, 4, 42, 56, xa.device, bf16)  # the plan forward() uses (keyed by the tensor's device)
+            plan._graph, plan._eager_runs, plan.use_graph = None, 0, True
+            ea, eb = m(xa), m(xb)          # two eager runs; the second one also captures
+            assert plan._graph is not None
+            ga, gb = m(xa), m(xb)          # replays
+            assert torch.equal(ea, ga) and torch.equal(eb, gb)
+            assert not torch.equal(ga, gb)
+
+
 @pytest.mark.parametrize("case", ["vits_n50_48x64", "vits_n23_40x90"])
 def test_driver_fp32_matches_reference_golden(case):
     g = np.load(os.path.join(GOLD, f"driver_{case}.npz"))

@@ -11,6 +11,7 @@ convolution carry a zero one-pixel border per frame ("padded", see include/vda.h
 from __future__ import annotations
 
 import ctypes as C
+import os
 import math
 
 import torch
@@ -163,6 +164,9 @@ class ForwardPlan:
         self._ws = None
         self._ws_need = 0
         self._lib = L.load()
+        self.use_graph = os.environ.get("VDA_NO_GRAPH", "0") != "1"
+        self._graph = None
+        self._eager_runs = 0
         self._build(skip_tmp_block)
         if not self.use_tc:
             self._ws = torch.empty(max(self._ws_need, 4), dtype=torch.uint8, device=device)
@@ -431,6 +435,24 @@ class ForwardPlan:
         return self.depth
 
     def launch(self):
+        """Enqueue the whole forward on the current stream.  After the first (eager) run the launch list is captured
+        into a CUDA graph and replayed: the list is static (fixed buffers, tensor maps passed by value), and for the
+        small encoders the ~270 ctypes calls per window otherwise cost as much host time as the GPU needs."""
+        if self._graph is not None:
+            self._graph.replay()
+            return
+        self._launch_ops()
+        self._eager_runs += 1
+        if self.use_graph and self._eager_runs == 2 and not torch.cuda.is_current_stream_capturing():
+            g = torch.cuda.CUDAGraph()
+            try:
+                with torch.cuda.graph(g):
+                    self._launch_ops()
+                self._graph = g
+            except Exception:  # capture is an optimisation: stay on the launch loop if the runtime refuses
+                self.use_graph = False
+
+    def _launch_ops(self):
         st = L.stream_ptr()
         lib = self._lib
         gemm = lib.vda_gemm
