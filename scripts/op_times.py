@@ -12,7 +12,7 @@ import torch
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), ".."))
 from video_depth_anything_b200 import lib as L  # noqa: E402
 from video_depth_anything_b200.engine import ForwardPlan, PackedWeights  # noqa: E402
-from video_depth_anything_b200.video_depth import VideoDepthAnything  # noqa: E402
+from bench import build_model  # noqa: E402
 
 
 def main():
@@ -26,7 +26,7 @@ def main():
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     torch.manual_seed(0)
-    model = VideoDepthAnything(encoder=a.encoder).to(dev)
+    model = build_model(a.encoder, dev)  # the shipped configuration of that encoder (features, out_channels)
     pw = PackedWeights(model, dev, bf16=True)
     plan = ForwardPlan(pw, 1, a.frames, a.size, a.size, dev)
     plan.x_in.normal_()
