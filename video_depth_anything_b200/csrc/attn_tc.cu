@@ -1,19 +1,24 @@
 // tcgen05 flash attention for the DINOv2 encoder (dinov2_layers/attention.py:49-59), head_dim 64, non-causal.
 //
-// One CTA = up to 256 query rows (two 128-row tiles) of one (frame, head); one CTA per SM.  The work of a CTA is cut
-// into FOUR independent streams (tile t, key half hh): stream (t, hh) runs an online softmax of tile t's rows over the
-// keys [128 j + 64 hh, +64) of every key block j, with its own S and O accumulators in TMEM, its own running max / sum
-// and its own MMA issuer, and the two halves of a tile are merged once, at the end (a two-way split-KV).
-//   warp 0      : TMA producer (Q tiles once, then K_j / V_j tiles of 128 keys through 3-stage rings)
-//   warps 1-4   : MMA issuer of stream w-1 (one thread each): S = Q_t K_j[hh]^T (128x64x64), O += P V_j[hh] (128x64x64)
-//   warps 5-20  : softmax, four warps per stream (one per TMEM lane quadrant); a thread owns one query row x 64 keys
+// One CTA = 128 query rows (one tile) of one (frame, head); TWO CTAs are resident per SM (256 TMEM columns, 112 KB of
+// shared memory and 11 warps each), so one CTA's prologue (barrier set-up, TMEM allocation, the first Q / K round trip)
+// and epilogue (merge, store, teardown) run under the other's main loop -- with one 256-row CTA per SM that per-CTA
+// overhead was a quarter of the kernel.  The work of a CTA is cut into TWO independent streams (key half hh): stream hh
+// runs an online softmax of the tile's rows over the keys [128 j + 64 hh, +64) of every key block j, with its own S and
+// O accumulators in TMEM, its own running max / sum and its own MMA issuer, and the halves are merged once, at the end
+// (a two-way split-KV).
+//   warp 0      : TMA producer (the Q tile once, then K_j / V_j tiles of 128 keys through 2-stage rings)
+//   warps 1-2   : MMA issuer of stream w-1 (one thread each): S = Q K_j[hh]^T (128x64x64), O += P V_j[hh] (128x64x64)
+//   warps 3-10  : softmax, four warps per stream (one per TMEM lane quadrant); a thread owns one query row x 64 keys
 // Why streams: a softmax warp's iteration is a CHAIN of waits (S ready -> TMEM read -> max -> 64 exponentials -> PV
 // done -> P store), and the exponentials (MUFU.EX2, 4 lanes/clk/scheduler: scripts/micro/xu_pipe.cu) are the busiest
 // unit.  With one issuer and an exchange of the row max between the key halves (the previous version) the sixteen
 // warps ran in lock step -- all four warps of a scheduler queued on the MUFU together, then left it idle together
 // (per-phase clock64 trace: 1750 clk in the exponentials with ~3.4 warps contending, 1750 clk outside them).
 // Independent streams have no per-block exchange and no in-order issue coupling, so they drift apart and one stream's
-// exponentials run under the others' waits.
+// exponentials run under the others' waits.  What bounds the loop now is instruction issue (the exponential phase is
+// ~290 instructions per warp and four softmax warps share a scheduler: replacing MUFU.EX2 by an FMA changes nothing)
+// and tcgen05.mma's ~48 clk floor per instruction at N = 64 (scripts/micro/mma_rate.cu).
 // A softmax thread reads its 64 scores out of TMEM ONCE, rounding to bf16 and packing as it goes (32 registers),
 // releases the S tile immediately (the next S MMA overlaps the exponentials), then: online max / sum in fp32, P
 // written to shared memory as the bf16 A operand of the PV MMA, O accumulated in TMEM across key blocks (rescaled
@@ -37,18 +42,19 @@ extern "C" int vda_debug_fa_trace(long long* out) { return (int)cudaMemcpyFromSy
 namespace {
 
 constexpr int BQ = 128, BKV = 128, HD = 64, KH = 64;  // KH: keys per stream and block
-constexpr int NS = 3;                  // K / V ring depth
+constexpr int NS = 2;                  // K / V ring depth
+constexpr int NSTREAM = 2;
 constexpr int TILE_BYTES = 128 * 128;  // 128 rows x 64 bf16
-constexpr int OFF_Q = 0;                         // 2 tiles
-constexpr int OFF_K = 2 * TILE_BYTES;            // NS tiles
+constexpr int OFF_Q = 0;                         // 1 tile; after the last S MMA it holds the (max, sum) exchange
+constexpr int OFF_K = TILE_BYTES;                // NS tiles
 constexpr int OFF_V = OFF_K + NS * TILE_BYTES;   // NS tiles
-constexpr int OFF_P = OFF_V + NS * TILE_BYTES;   // 4 streams x (128 rows x 64 keys)
-constexpr int OFF_BAR = OFF_P + 4 * TILE_BYTES;
-constexpr int OFF_X = OFF_BAR + 256;             // (max, sum) exchange between the two halves of a tile: 4 KB
-constexpr int FA_SMEM = OFF_X + 4 * 1024;
-constexpr int FA_WARPS = 1 + 4 + 16;
+constexpr int OFF_P = OFF_V + NS * TILE_BYTES;   // 2 streams x (128 rows x 64 keys)
+constexpr int OFF_BAR = OFF_P + NSTREAM * TILE_BYTES;
+constexpr int OFF_X = OFF_Q;
+constexpr int FA_SMEM = OFF_BAR + 256;           // 112.25 KB: two CTAs per SM (228 KB, 1 KB reserved per CTA)
+constexpr int FA_WARPS = 1 + NSTREAM + 4 * NSTREAM;
 constexpr int FA_THREADS = FA_WARPS * 32;
-constexpr uint32_t TM_S = 0, TM_O = 256, TM_COLS = 512;  // S of stream s at TM_S + 64 s, O at TM_O + 64 s
+constexpr uint32_t TM_S = 0, TM_O = 128, TM_COLS = 256;  // S of stream s at TM_S + 64 s, O at TM_O + 64 s
 
 // barrier indices
 constexpr int B_QFULL = 0;               // 1
@@ -56,13 +62,14 @@ constexpr int B_KFULL = 1;               // NS
 constexpr int B_KEMPTY = B_KFULL + NS;   // NS
 constexpr int B_VFULL = B_KEMPTY + NS;   // NS
 constexpr int B_VEMPTY = B_VFULL + NS;   // NS
-constexpr int B_SFULL = B_VEMPTY + NS;   // 4
-constexpr int B_SFREE = B_SFULL + 4;     // 4
-constexpr int B_PFULL = B_SFREE + 4;     // 4
-constexpr int B_PVDONE = B_PFULL + 4;    // 4
-constexpr int NBARS = B_PVDONE + 4;
+constexpr int B_SFULL = B_VEMPTY + NS;         // per stream
+constexpr int B_SFREE = B_SFULL + NSTREAM;
+constexpr int B_PFULL = B_SFREE + NSTREAM;
+constexpr int B_PVDONE = B_PFULL + NSTREAM;
+constexpr int B_QFREE = B_PVDONE + NSTREAM;    // 1: every S MMA has read Q (its tile then carries the final exchange)
+constexpr int NBARS = B_QFREE + 1;
 static_assert(NBARS * 8 + 8 <= 256, "barrier area");
-static_assert(FA_SMEM <= 232448, "shared memory budget");
+static_assert(2 * (FA_SMEM + 1024) <= 233472, "two CTAs per SM");
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
@@ -75,16 +82,15 @@ __device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
   return r;
 }
 
-__global__ void __launch_bounds__(FA_THREADS, 1)
+__global__ void __launch_bounds__(FA_THREADS, 2)
 flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ o, int ntok, int heads) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + NBARS);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * 2 * BQ, h = blockIdx.y, f = blockIdx.z;
+  const int q0 = blockIdx.x * BQ, h = blockIdx.y, f = blockIdx.z;
   const int D = heads * HD;
   const int nblk = (ntok + BKV - 1) / BKV;
-  const int ntiles = (q0 + BQ < ntok) ? 2 : 1;  // the last CTA of a frame may own a single tile
   const int row0 = f * ntok;                    // first row of this frame in the [frames*ntok, 3D] matrix
 
   if (threadIdx.x == 0) {
@@ -96,11 +102,12 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
     ptx::mbar_init(&bars[B_QFULL], 1);
     for (int s = 0; s < NS; ++s) {
       ptx::mbar_init(&bars[B_KFULL + s], 1);
-      ptx::mbar_init(&bars[B_KEMPTY + s], 2 * ntiles);  // one commit per active stream
+      ptx::mbar_init(&bars[B_KEMPTY + s], NSTREAM);  // one commit per stream
       ptx::mbar_init(&bars[B_VFULL + s], 1);
-      ptx::mbar_init(&bars[B_VEMPTY + s], 2 * ntiles);
+      ptx::mbar_init(&bars[B_VEMPTY + s], NSTREAM);
     }
-    for (int s = 0; s < 4; ++s) {
+    ptx::mbar_init(&bars[B_QFREE], NSTREAM);
+    for (int s = 0; s < NSTREAM; ++s) {
       ptx::mbar_init(&bars[B_SFULL + s], 1);
       ptx::mbar_init(&bars[B_SFREE + s], 4);
       ptx::mbar_init(&bars[B_PFULL + s], 4);
@@ -120,9 +127,8 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      ptx::mbar_arrive_expect_tx(&bars[B_QFULL], ntiles * TILE_BYTES);
-      for (int t = 0; t < ntiles; ++t)
-        ptx::tma_load_2d(smem + OFF_Q + t * TILE_BYTES, &tm, h * HD, row0 + q0 + t * BQ, &bars[B_QFULL]);
+      ptx::mbar_arrive_expect_tx(&bars[B_QFULL], TILE_BYTES);
+      ptx::tma_load_2d(smem + OFF_Q, &tm, h * HD, row0 + q0, &bars[B_QFULL]);
       for (int j = 0; j < nblk; ++j) {
         const int s = j % NS;
         const uint32_t ph = (j / NS) & 1;
@@ -134,13 +140,13 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         ptx::tma_load_2d(smem + OFF_V + s * TILE_BYTES, &tm, 2 * D + h * HD, row0 + j * BKV, &bars[B_VFULL + s]);
       }
     }
-  } else if (warp <= 4) {
+  } else if (warp <= NSTREAM) {
     // ------------------------------------------------------------------ MMA issuer of stream warp-1
-    const int sid = warp - 1, t = sid >> 1, hh = sid & 1;
-    if (lane == 0 && t < ntiles) {
+    const int sid = warp - 1, hh = sid;
+    if (lane == 0) {
       constexpr uint32_t idesc_s = ptx::make_idesc_bf16(BQ, KH, 0, 0);
       constexpr uint32_t idesc_pv = ptx::make_idesc_bf16(BQ, HD, 0, 1);  // B = V is MN-major (d contiguous)
-      const uint64_t dq = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_Q + t * TILE_BYTES), 16, 1024);
+      const uint64_t dq = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_Q), 16, 1024);
       const uint64_t dp = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_P + sid * TILE_BYTES), 16, 1024);
       const uint32_t ds_tmem = tmem + TM_S + sid * KH, do_tmem = tmem + TM_O + sid * HD;
       auto issue_s = [&](int j) {  // S(j) of this stream: keys [64 hh, +64) of block j are rows 64 hh.. of the K tile
@@ -153,6 +159,7 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         for (int k = 0; k < HD / 16; ++k) ptx::mma_f16_ss(ds_tmem, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
         ptx::tc_commit(&bars[B_SFULL + sid]);
         ptx::tc_commit(&bars[B_KEMPTY + s]);
+        if (j == nblk - 1) ptx::tc_commit(&bars[B_QFREE]);
       };
       ptx::mbar_wait(&bars[B_QFULL], 0);
       issue_s(0);
@@ -173,9 +180,9 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
       }
     }
   } else {
-    // ------------------------------------------------------------------ softmax warps: stream (warp-5)/4, TMEM lane quadrant warp%4
-    const int sid = (warp - 5) >> 2, t = sid >> 1, hh = sid & 1;
-    if (t < ntiles) {
+    // ------------------------------------------------------------------ softmax warps: stream (warp-3)/4, TMEM lane quadrant warp%4
+    const int sid = (warp - 1 - NSTREAM) >> 2, hh = sid;
+    {
       const int q = warp & 3;       // TMEM lane quadrant this warp may access
       const int r = q * 32 + lane;  // query row inside the tile == TMEM lane
       const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
@@ -275,10 +282,11 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
       ptx::tc_fence_after();
       // ---- merge the two key halves of the tile: exchange (m, l) with the partner stream's warp of the same quadrant;
       // after the barrier the partner has seen its own last PV complete, so both O accumulators are final
-      float2* xs = reinterpret_cast<float2*>(smem + OFF_X) + (t * 2) * 128;
+      ptx::mbar_wait(&bars[B_QFREE], 0);  // both streams' last S MMAs have read Q: its tile is free for the exchange
+      float2* xs = reinterpret_cast<float2*>(smem + OFF_X);
       xs[hh * 128 + r] = make_float2(m, l);
       ptx::tc_fence_before();
-      asm volatile("bar.sync %0, 64;" ::"r"(1 + t * 4 + q) : "memory");
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
       ptx::tc_fence_after();
       const float2 pml = xs[(hh ^ 1) * 128 + r];
       const float mm = fmaxf(m, pml.x);  // finite: block 0 of key half 0 always holds a key of the frame
@@ -311,7 +319,7 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
 #pragma unroll
       for (int it = 0; it < 4; ++it) {
         const int rr = 8 * it + (lane >> 2);
-        const int qrow = q0 + t * BQ + q * 32 + rr;
+        const int qrow = q0 + q * 32 + rr;
         const uint4 u = *reinterpret_cast<const uint4*>(wst + rr * 64 + ((g ^ ((rr >> 1) & 3)) << 4));
         if (qrow < ntok) *reinterpret_cast<uint4*>(o + ((long long)row0 + qrow) * D + h * HD + hh * 32 + 8 * g) = u;
       }
@@ -341,7 +349,7 @@ int vda_attention_tc(const void* qkv, void* o, int frames, int ntok, int heads, 
     }
     attr_set = true;
   }
-  dim3 grid((ntok + 2 * BQ - 1) / (2 * BQ), heads, frames);
+  dim3 grid((ntok + BQ - 1) / BQ, heads, frames);
   flash_attn_tc_kernel<<<grid, FA_THREADS, FA_SMEM, st>>>(tm, reinterpret_cast<bf16*>(o), ntok, heads);
   VDA_CUDA_LAUNCH_CHECK("flash_attn_tc_kernel");
   return 0;
