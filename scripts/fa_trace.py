@@ -18,12 +18,13 @@ for _ in range(3):
     L.check(lib.vda_attention(qkv.data_ptr(), o.data_ptr(), L.BF16, frames, ntok, heads, 1, 1, L.stream_ptr()), "attn")
 torch.cuda.synchronize()
 buf = (C.c_longlong * (4 * 16 * 8))()
+NSTREAM = 2  # streams per CTA (key halves)
 raw = C.CDLL(lib._name)
 print("rc", raw.vda_debug_fa_trace(buf))
 names = ["loop", "S ready", "read+pack", "max", "exp", "PVdone", "store+arrive"]
-t0 = min(buf[(w * 16 + 2) * 8] for w in range(4))
+t0 = min(buf[(w * 16 + 2) * 8] for w in range(NSTREAM))
 for j in range(2, 9):
-    for w in range(4):
+    for w in range(NSTREAM):
         ev = [buf[(w * 16 + j) * 8 + e] for e in range(7)]
         d = [ev[i + 1] - ev[i] for i in range(6)]
         print(f"j={j} stream{w} start={ev[0] - t0:6d}  " + "  ".join(f"{n}={x:5d}" for n, x in zip(names[1:], d)) +

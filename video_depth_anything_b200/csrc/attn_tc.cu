@@ -33,7 +33,7 @@
 
 #ifdef FA_TRACE  // per-phase clock64 timeline of the four softmax warps of one scheduler (scripts/fa_trace.py); debugging aid
 __device__ long long g_fa_trace[4 * 16 * 8];  // [stream][block j][event]
-#define FA_T(ev) do { if (blockIdx.x == 2 && blockIdx.y == 5 && blockIdx.z == 7 && q == 2 && lane == 0 && j < 16) \
+#define FA_T(ev) do { if (blockIdx.x == 4 && blockIdx.y == 5 && blockIdx.z == 7 && q == 2 && lane == 0 && j < 16) \
                         g_fa_trace[(sid * 16 + j) * 8 + (ev)] = clock64(); } while (0)
 extern "C" int vda_debug_fa_trace(long long* out) { return (int)cudaMemcpyFromSymbol(out, g_fa_trace, sizeof(g_fa_trace)); }
 #else
