@@ -138,7 +138,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--encoder", default="vitl", choices=["vitl", "vits"])
     ap.add_argument("--size", type=int, default=518)
-    ap.add_argument("--cpu-sample-frames", type=int, default=2)
+    ap.add_argument("--cpu-sample-frames", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -280,7 +280,7 @@ def main():
                     e2e={"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": x_host.numel() * 4,
                          "d2h_bytes_per_step": out_host.numel() * 4},
                     gpu_launches=plan.n_launches * a.steps,
-                    roofline={"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05; encoder qkv/proj/fc1/fc2)",
+                    roofline={"bound": "tensor", "kernel": "gemm_tc2_kernel (tcgen05 cta_group::2 pair GEMM; encoder qkv/proj/fc1/fc2)",
                               "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": measured_traffic(),
                               "peak_source": which, "launches_per_step": len(enc_gemm), "tflop_per_step": flops_per_step / 1e12,
                               "share_of_step": gemm_ms / ms_total})
