@@ -14,7 +14,7 @@ lib = L.load()
 M = 43840
 shapes = [("qkv", 3072, 1024, "store"), ("proj", 1024, 1024, "resid"), ("fc1", 4096, 1024, "gelu"), ("fc2", 1024, 4096, "resid"),
           ("projS", 1024, 1024, "store"), ("fc2S", 1024, 4096, "store"), ("projRelu", 1024, 1024, "relu2"),
-          ("projRes", 1024, 1024, "res"), ("projResIn", 1024, 1024, "resin"), ("mmRes", 256, 256, "res"), ("mmS", 256, 256, "store")]
+          ("projRes", 1024, 1024, "res"), ("projResIn", 1024, 1024, "resin"), ("mmRes", 256, 256, "res"), ("mmS", 256, 256, "store"), ("fc1S", 4096, 1024, "store")]
 if len(sys.argv) > 1:
     shapes = [s for s in shapes if s[0] in sys.argv[1:]]
 for name, N, K, kind in shapes:
