@@ -153,6 +153,15 @@ int vda_bilinear(const void* in, int32_t in_dtype, void* out, int32_t out_dtype,
 int vda_output_head(const void* x, const float* w, const float* bias, const float* head_w, float head_b, float* depth,
                     int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow, vda_stream_t stream);
 
+/* The same head with the 3x3 conv's operands in IEEE fp16 (tcgen05 kind::f16, K = 16 per MMA: half the MMAs of the TF32
+ * form).  w_f16[32, 9*C] is the fp32 weight rounded to nearest fp16 by the caller; the interpolated activations are
+ * rounded to nearest fp16 in the kernel (saturating at +-65504).  fp16 carries the 10 explicit mantissa bits TF32 does,
+ * so the products are those of the TF32 conv up to round-to-nearest vs. truncation of the operands; accumulation is
+ * fp32.  C must be a multiple of 64. */
+int vda_output_head_f16(const void* x, const void* w_f16, const float* bias, const float* head_w, float head_b,
+                        float* depth, int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow,
+                        vda_stream_t stream);
+
 /* Patch-embed im2col (patch_embed.py:76): x[frames,3,H,W] f32 -> A[frames*(H/14)*(W/14), kpad] (k = c*196+i*14+j; pad = 0). */
 int vda_im2col_patch(const float* x, void* A, int32_t a_dtype, int32_t frames, int32_t H, int32_t W, int32_t kpad,
                      vda_stream_t stream);

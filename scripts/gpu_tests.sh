@@ -12,6 +12,7 @@ run kernels 600 tests/test_gpu_kernels.py
 run tc_gemm 300 tests/test_gpu_tc.py::test_gemm_tc_bias
 run tc_epi 300 tests/test_gpu_tc.py::test_gemm_tc_epilogues
 run tc_conv 300 tests/test_gpu_tc.py::test_conv3x3_tc tests/test_gpu_tc.py::test_output_head_tc_tf32
+run tc_head 300 tests/test_gpu_tc.py::test_output_head_fused tests/test_gpu_tc.py::test_output_head_fused_f16
 run tc_attn 300 tests/test_gpu_tc.py::test_flash_attention_tc
 run fwd_fp32 900 tests/test_gpu_forward.py -k "(fp32 or taps or contract) and not driver"
 run fwd_bf16 900 tests/test_gpu_forward.py -k "bf16 and not driver"

@@ -187,3 +187,39 @@ def test_output_head_fused(Ci, ih, iw, oh, ow, frames):
              head_w=hw_, head_out=ho, head_b=hb, use_tc=1)
     s2 = stats("head_fused_vs_unfused", depth.reshape(-1), ho)
     assert s2["max_rel_to_peak"] < 1e-3
+
+
+@pytest.mark.parametrize("Ci,ih,iw,oh,ow,frames", [(64, 9, 7, 21, 13, 1), (128, 32, 48, 56, 84, 3), (128, 40, 40, 70, 70, 2),
+                                                   (192, 12, 20, 30, 37, 2)])
+def test_output_head_fused_f16(Ci, ih, iw, oh, ow, frames):
+    """vda_output_head_f16 (fp16 operands, 64 channels per chunk): same bar against fp64 torch as the TF32 form, and no
+    farther from it than the TF32 form is; saturates instead of overflowing."""
+    from video_depth_anything_b200.engine import _conv3x3_pack
+    L, lib = _lib()
+    torch.manual_seed(Ci + oh)
+    x = torch.randn(frames, Ci, ih, iw, device=dev).bfloat16()
+    w = torch.randn(32, Ci, 3, 3, device=dev) / (9 * Ci) ** 0.5
+    b, hw_, hb = torch.randn(32, device=dev) * 0.1, torch.randn(32, device=dev).abs(), 0.05
+    xd = x.permute(0, 2, 3, 1).reshape(-1, Ci).contiguous()
+    wp = _conv3x3_pack(w)
+    wh = wp.to(torch.float16).contiguous()
+    depth = torch.full((frames, oh, ow), float("nan"), device=dev)
+    L.check(lib.vda_output_head_f16(xd.data_ptr(), wh.data_ptr(), b.data_ptr(), hw_.data_ptr(), hb, depth.data_ptr(), frames,
+                                    ih, iw, Ci, oh, ow, L.stream_ptr()), "vda_output_head_f16")
+    d32 = torch.empty_like(depth)
+    L.check(lib.vda_output_head(xd.data_ptr(), wp.data_ptr(), b.data_ptr(), hw_.data_ptr(), hb, d32.data_ptr(), frames, ih, iw,
+                                Ci, oh, ow, L.stream_ptr()), "vda_output_head")
+    torch.cuda.synchronize()
+    up = F.interpolate(x.double(), (oh, ow), mode="bilinear", align_corners=True)
+    ref = F.relu(F.conv2d(F.relu(F.conv2d(up, w.double(), b.double(), padding=1)), hw_.double().reshape(1, 32, 1, 1),
+                          torch.tensor([hb], device=dev, dtype=torch.float64)))
+    s = stats(f"head_f16_{Ci}_{oh}x{ow}", depth.reshape(frames, 1, oh, ow), ref)
+    s32 = stats(f"head_tf32_{Ci}_{oh}x{ow}", d32.reshape(frames, 1, oh, ow), ref)
+    assert s["max_rel_to_peak"] < 2e-3 and s["mean_abs"] < 3e-4 * s["ref_peak"]
+    assert s["mean_abs"] <= 1.1 * s32["mean_abs"]  # round-to-nearest operands: at least as close as the truncating TF32 path
+    # out-of-range activations saturate (no inf / nan in the depth map)
+    xd2 = (xd.float() * 3e4).bfloat16()
+    L.check(lib.vda_output_head_f16(xd2.data_ptr(), wh.data_ptr(), b.data_ptr(), hw_.data_ptr(), hb, depth.data_ptr(), frames,
+                                    ih, iw, Ci, oh, ow, L.stream_ptr()), "vda_output_head_f16")
+    torch.cuda.synchronize()
+    assert torch.isfinite(depth).all()

@@ -28,8 +28,8 @@ constexpr int PW = TW + 2;                // halo width
 constexpr int HP = (TH + 2) * PW;         // 180 halo pixels
 constexpr int HPP = 185;                  // padded: slab stride = 16 (mod 128) bytes -> conflict-free stores
 constexpr int SLAB = HPP * 16;            // bytes per 4-channel slab
-constexpr int KC = 32;                    // channels per chunk
-constexpr int ABUF = (KC / 4) * SLAB;     // 23680 B
+constexpr int NSLAB = 8;                  // 16-byte channel slabs per chunk: 32 fp32 channels, or 64 fp16 channels
+constexpr int ABUF = NSLAB * SLAB;        // 23680 B
 constexpr int NABUF = 4;
 constexpr int BBUF = 9 * 4096;            // one chunk of the weights: 9 taps x [32 rows x 128 B]
 constexpr int NBBUF = 2;
@@ -62,6 +62,12 @@ struct HtArgs {
 };
 
 // K-major, no swizzle: LBO = distance between core matrices along K, SBO = distance between 8-row groups along M.
+__device__ __forceinline__ uint32_t pack_f16x2_sat(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
 __device__ __forceinline__ uint64_t make_noswz_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
@@ -71,6 +77,10 @@ __device__ __forceinline__ uint64_t make_noswz_desc(uint32_t smem_addr, uint32_t
   return d;
 }
 
+// H = false: fp32 operands, kind::tf32 (K = 8 per MMA, 32 channels per chunk).
+// H = true:  fp16 operands, kind::f16 (K = 16 per MMA, 64 channels per chunk): the same 10-bit mantissa as TF32, rounded
+//            to nearest instead of truncated, half as many MMAs.  Conversions saturate at +-65504.
+template <bool H>
 __global__ void __launch_bounds__(HT_THREADS, 1)
 head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -78,6 +88,7 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + HT_NBARS);
   float* spar = reinterpret_cast<float*>(smem + OFF_PAR);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int KC = H ? 64 : 32;  // channels per chunk
 
   if (threadIdx.x == 0) {
     if (ptx::smem_u32(smem) & 1023) {
@@ -141,10 +152,10 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
             wts[j][0] = wts[j][1] = wts[j][2] = wts[j][3] = 0.f;
             raw[j][0] = raw[j][1] = raw[j][2] = raw[j][3] = make_uint4(0, 0, 0, 0);
             if (it < NITEMS) {
-              const int p = it >> 2, cg = it & 3;
+              const int p = it / (KC / 8), cg = it % (KC / 8);
               const int hy = p / PW, hx = p - hy * PW;
               const int oy = ty0 + hy - 1, ox = tx0 + hx - 1;
-              dsto[j] = (2 * cg) * SLAB + p * 16;
+              dsto[j] = (H ? cg : 2 * cg) * SLAB + p * 16;
               if (oy >= 0 && oy < a.oh && ox >= 0 && ox < a.ow) {
                 const float h1r = a.rh * oy;
                 const int h1 = (int)h1r;
@@ -180,8 +191,13 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
                              h1l * (w0l * bf16hi_to_f32(rc[i]) + w1l * bf16hi_to_f32(rd[i]));
             }
             uint8_t* dst = abuf + dsto[j];
-            *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
-            *reinterpret_cast<float4*>(dst + SLAB) = make_float4(o[4], o[5], o[6], o[7]);
+            if (H) {
+              *reinterpret_cast<uint4*>(dst) = make_uint4(pack_f16x2_sat(o[0], o[1]), pack_f16x2_sat(o[2], o[3]),
+                                                          pack_f16x2_sat(o[4], o[5]), pack_f16x2_sat(o[6], o[7]));
+            } else {
+              *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+              *reinterpret_cast<float4*>(dst + SLAB) = make_float4(o[4], o[5], o[6], o[7]);
+            }
           }
           }
           ptx::fence_proxy_async();
@@ -207,7 +223,7 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
   } else if (warp == NPROD_WARPS + 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_tf32(128, NOUT);
+      constexpr uint32_t idesc = H ? ptx::make_idesc_f16(128, NOUT) : ptx::make_idesc_tf32(128, NOUT);
       uint32_t acnt = 0, bcnt = 0, gcnt = 0;
       for (int g = blockIdx.x; g < a.ngroups; g += gridDim.x, ++gcnt) {
         const int nt = min(GROUP, a.total_tiles - g * GROUP);
@@ -229,9 +245,10 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
               const uint32_t a0 = sa + ((tap / 3) * PW + (tap % 3)) * 16;  // halo pixel (1+dy, 1+dx), dy,dx = tap/3-1, tap%3-1
               const uint64_t db = ptx::make_sw128_desc(sb + tap * 4096, 16, 1024);
 #pragma unroll
-              for (int kk = 0; kk < KC / 8; ++kk) {
+              for (int kk = 0; kk < NSLAB / 2; ++kk) {  // one MMA covers two slabs (K = 8 fp32 or 16 fp16) = 32 B of a weight row
                 const uint64_t da = make_noswz_desc(a0 + (2 * kk) * SLAB, SLAB, PW * 16);
-                ptx::mma_tf32_ss(d_tmem, da, db + 2 * kk, idesc, (kc | tap | kk) != 0);
+                if (H) ptx::mma_f16_ss(d_tmem, da, db + 2 * kk, idesc, (kc | tap | kk) != 0);
+                else ptx::mma_tf32_ss(d_tmem, da, db + 2 * kk, idesc, (kc | tap | kk) != 0);
               }
             }
             ptx::tc_commit(&bars[BA_EMPTY + ab]);
@@ -286,15 +303,16 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
 
 }  // namespace
 
-extern "C" int vda_output_head(const void* x, const float* w, const float* bias, const float* head_w, float head_b,
-                               float* depth, int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow,
-                               vda_stream_t stream) {
-  VDA_CHECK_ARG(C >= KC && C % KC == 0, "vda_output_head: C=%d must be a multiple of 32", C);
+template <bool H>
+static int launch_head(const void* x, const void* w, const float* bias, const float* head_w, float head_b, float* depth,
+                       int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow, vda_stream_t stream) {
+  constexpr int KC = H ? 64 : 32, ES = H ? 2 : 4;
+  VDA_CHECK_ARG(C >= KC && C % KC == 0, "vda_output_head%s: C=%d must be a multiple of %d", H ? "_f16" : "", C, KC);
   VDA_CHECK_ARG(frames > 0 && ih > 0 && iw > 0 && oh > 0 && ow > 0, "vda_output_head: bad geometry");
   VDA_CHECK_ARG(((uintptr_t)x % 16) == 0 && ((uintptr_t)w % 16) == 0, "vda_output_head: x / w must be 16B aligned");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   CUtensorMap tmW;
-  int rc = vda_make_tmap_2d(&tmW, w, (uint64_t)9 * C, NOUT, (uint64_t)9 * C * 4, 32, NOUT, 4);
+  int rc = vda_make_tmap_2d(&tmW, w, (uint64_t)9 * C, NOUT, (uint64_t)9 * C * ES, KC, NOUT, ES);
   if (rc) return rc;
   HtArgs a;
   a.x = reinterpret_cast<const bf16*>(x);
@@ -309,7 +327,7 @@ extern "C" int vda_output_head(const void* x, const float* w, const float* bias,
   a.nkc = C / KC;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t ce = cudaFuncSetAttribute(head_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HT_SMEM);
+    cudaError_t ce = cudaFuncSetAttribute(head_tail_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, HT_SMEM);
     if (ce != cudaSuccess) {
       vda_set_error("head_tail: cudaFuncSetAttribute(%d) failed: %s", HT_SMEM, cudaGetErrorString(ce));
       return (int)ce;
@@ -317,7 +335,19 @@ extern "C" int vda_output_head(const void* x, const float* w, const float* bias,
     attr_set = true;
   }
   const int grid = a.ngroups < vda_sm_count() ? a.ngroups : vda_sm_count();
-  head_tail_kernel<<<grid, HT_THREADS, HT_SMEM, st>>>(tmW, a);
+  head_tail_kernel<H><<<grid, HT_THREADS, HT_SMEM, st>>>(tmW, a);
   VDA_CUDA_LAUNCH_CHECK("head_tail_kernel");
   return 0;
+}
+
+extern "C" int vda_output_head(const void* x, const float* w, const float* bias, const float* head_w, float head_b,
+                               float* depth, int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow,
+                               vda_stream_t stream) {
+  return launch_head<false>(x, w, bias, head_w, head_b, depth, frames, ih, iw, C, oh, ow, stream);
+}
+
+extern "C" int vda_output_head_f16(const void* x, const void* w_f16, const float* bias, const float* head_w, float head_b,
+                                   float* depth, int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh,
+                                   int32_t ow, vda_stream_t stream) {
+  return launch_head<true>(x, w_f16, bias, head_w, head_b, depth, frames, ih, iw, C, oh, ow, stream);
 }

@@ -109,6 +109,7 @@ class PackedWeights:
         # the fp32 island (dpt_temporal.py:95-97): weights stay fp32 (tcgen05 kind::tf32 in the bf16 build)
         w2 = _conv3x3_pack(sd[sc + "output_conv2.0.weight"]).float()
         w["oc2.w32"] = w2.contiguous()
+        w["oc2.w16"] = w2.to(torch.float16).contiguous()  # operands of vda_output_head_f16 (round to nearest, 10-bit mantissa like TF32)
         vec("oc2.b", sd[sc + "output_conv2.0.bias"])
         vec("oc2.hw", sd[sc + "output_conv2.2.weight"].reshape(32))
         self.head_b = float(sd[sc + "output_conv2.2.bias"].reshape(()).item())
@@ -416,7 +417,9 @@ class ForwardPlan:
         self.bufs["depth"] = depth
         if self.use_tc and self.fused_tail and (F // 2) % 32 == 0:
             # bf16 build: interpolation, TF32 tensor-core conv and the ReLU -> 1x1 -> ReLU tail in one kernel
-            self.op(lib.vda_output_head, o1.data_ptr(), W_["oc2.w32"].data_ptr(), W_["oc2.b"].data_ptr(), W_["oc2.hw"].data_ptr(),
+            half = (F // 2) % 64 == 0 and os.environ.get("VDA_HEAD_TF32", "0") != "1"
+            self.op(lib.vda_output_head_f16 if half else lib.vda_output_head, o1.data_ptr(),
+                    W_["oc2.w16" if half else "oc2.w32"].data_ptr(), W_["oc2.b"].data_ptr(), W_["oc2.hw"].data_ptr(),
                     float(pw.head_b), depth.data_ptr(), BT, h0, w0, F // 2, self.H, self.W)
         else:
             up = self.buf("up", BT * (self.H + 2) * (self.W + 2), F // 2, torch.float32, zero=True)
