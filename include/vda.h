@@ -140,6 +140,13 @@ int vda_attention(const void* qkv, void* o, int32_t dtype, int32_t frames, int32
 int vda_temporal_attention(const void* qkv, void* o, int32_t dtype, int32_t batch, int32_t T, int32_t hw, int32_t C,
                            int32_t heads, int32_t round_bf16, vda_stream_t stream);
 
+/* Rotary position embedding of the temporal attention, pe='rope' (motion_module/attention.py:403-429, applied to query
+ * and key at motion_module.py:290-293 before the head split): columns [0, 2C) of qkv[rows, 3C] are rotated in place,
+ * pair (2i, 2i+1) of row r by the angle t*theta_i with t = (r / hw) % T, in fp32, result rounded to the activation type.
+ * tab[T, C] holds (cos, sin)(t*theta_i) interleaved -- the caller's `freqs_cis` (precompute_freqs_cis, :403-408). */
+int vda_rope_qk(void* qkv, int32_t dtype, const float* tab, int64_t rows, int32_t hw, int32_t T, int32_t C,
+                int32_t round_bf16, vda_stream_t stream);
+
 /* Bilinear resize, align_corners=True (blocks.py:156-158, dpt_temporal.py:92-94), channels-last.  Under CUDA autocast
  * upsample_bilinear2d is an fp32 op: bf16 in -> fp32 out is the un-rounded form the output head consumes. */
 int vda_bilinear(const void* in, int32_t in_dtype, void* out, int32_t out_dtype, int32_t frames, int32_t ih, int32_t iw,

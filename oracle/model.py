@@ -95,16 +95,37 @@ def encoder_taps(sd, x: torch.Tensor, encoder: str, collect=None):
 
 
 # --------------------------------------------------------------------------- motion module
+def rope_freqs_cis(dim: int, end: int, theta: float = 10000.0) -> torch.Tensor:
+    """`precompute_freqs_cis`, motion_module/attention.py:403-408 (complex64 [end, dim/2])."""
+    freqs = 1.0 / (theta ** (torch.arange(0, dim, 2)[: (dim // 2)].float() / dim))
+    t = torch.arange(end, dtype=torch.float32)
+    return torch.polar(torch.ones(end, dim // 2), torch.outer(t, freqs))
+
+
+def rope_rotate(x: torch.Tensor, freqs_cis: torch.Tensor) -> torch.Tensor:
+    """`apply_rotary_emb` for one operand, motion_module/attention.py:419-429: x [n, T, c] viewed as c/2 complex
+    numbers per (n, t), multiplied by freqs_cis[t] in fp32, cast back to x's dtype."""
+    xc = torch.view_as_complex(x.float().reshape(*x.shape[:-1], -1, 2).contiguous())
+    return torch.view_as_real(xc * freqs_cis.view(1, xc.shape[1], xc.shape[2])).flatten(2).type_as(x)
+
+
 def temporal_attention(sd, p: str, h: torch.Tensor, T: int, heads: int = 8) -> torch.Tensor:
-    """motion_module.py:247-335 (APE path) + attention.py:93-111,182-211.  h: [(b f), d, c]."""
+    """motion_module.py:247-335 + attention.py:93-111,182-211.  h: [(b f), d, c].  The positional scheme follows the
+    state dict: a `pos_encoder.pe` buffer means pe='ape' (added to the input, :255-256); its absence means pe='rope'
+    (query and key rotated after their projections, :290-293)."""
     BF, d, c = h.shape
     b = BF // T
     h = h.reshape(b, T, d, c).permute(0, 2, 1, 3).reshape(b * d, T, c)  # "(b f) d c -> (b d) f c"
-    pe = sd[p + "pos_encoder.pe"]
-    h = h + pe[:, :T].to(h.dtype)
+    ape = (p + "pos_encoder.pe") in sd
+    if ape:
+        pe = sd[p + "pos_encoder.pe"]
+        h = h + pe[:, :T].to(h.dtype)
     q = F.linear(h, sd[p + "to_q.weight"])
     k = F.linear(h, sd[p + "to_k.weight"])
     v = F.linear(h, sd[p + "to_v.weight"])
+    if not ape:
+        fc = rope_freqs_cis(c, T).to(q.device)  # == precompute_freqs_cis(c, temporal_max_len)[:T]
+        q, k = rope_rotate(q, fc), rope_rotate(k, fc)
     dh = c // heads
 
     def split(t):

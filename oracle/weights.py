@@ -40,8 +40,9 @@ ENCODER_DIMS = {
 }
 
 
-def param_spec(encoder: str, num_frames: int = 32) -> "OrderedDict[str, tuple]":
-    """name -> shape for every state-dict entry, in the reference's own order."""
+def param_spec(encoder: str, num_frames: int = 32, pe: str = "ape") -> "OrderedDict[str, tuple]":
+    """name -> shape for every state-dict entry, in the reference's own order.  pe='rope' models have no
+    `pos_encoder.pe` buffers: freqs_cis is a plain attribute (motion_module.py:226-240)."""
     cfg = MODEL_CONFIGS[encoder]
     enc = ENCODER_DIMS[encoder]
     D, depth = enc["dim"], enc["depth"]
@@ -114,7 +115,8 @@ def param_spec(encoder: str, num_frames: int = 32) -> "OrderedDict[str, tuple]":
             s[ab + "to_v.weight"] = (C, C)
             s[ab + "to_out.0.weight"] = (C, C)
             s[ab + "to_out.0.bias"] = (C,)
-            s[ab + "pos_encoder.pe"] = (1, num_frames, C)
+            if pe == "ape":
+                s[ab + "pos_encoder.pe"] = (1, num_frames, C)
         for a in (0, 1):
             s[f"{tb}norms.{a}.weight"] = (C,)
             s[f"{tb}norms.{a}.bias"] = (C,)
@@ -145,7 +147,7 @@ def _gen(name: str, seed: int) -> torch.Generator:
     return g
 
 
-def make_state_dict(encoder: str, seed: int = 0, num_frames: int = 32) -> "OrderedDict[str, torch.Tensor]":
+def make_state_dict(encoder: str, seed: int = 0, num_frames: int = 32, pe: str = "ape") -> "OrderedDict[str, torch.Tensor]":
     """The fixed-seed weight recipe, fp32 CPU tensors.
 
     Weights ~ N(0, g/sqrt(fan_in)); biases ~ N(0, 0.05); every norm gets a
@@ -153,7 +155,7 @@ def make_state_dict(encoder: str, seed: int = 0, num_frames: int = 32) -> "Order
     the last 1x1 conv is mostly positive so the depth map is not half zeros.
     """
     sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
-    for name, shape in param_spec(encoder, num_frames).items():
+    for name, shape in param_spec(encoder, num_frames, pe).items():
         g = _gen(name, seed)
         leaf = name.rsplit(".", 1)[-1]
         if leaf == "pe":

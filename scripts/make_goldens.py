@@ -46,16 +46,17 @@ torch.set_num_threads(os.cpu_count())
 manifest = {"torch": torch.__version__, "numpy": np.__version__, "cases": {}}
 
 
-def ref_model(encoder, num_frames=32):
-    m = VideoDepthAnything(**MODEL_CONFIGS[encoder], num_frames=num_frames)
-    sd = make_state_dict(encoder, seed=0, num_frames=num_frames)
+def ref_model(encoder, num_frames=32, pe="ape"):
+    m = VideoDepthAnything(**MODEL_CONFIGS[encoder], num_frames=num_frames, pe=pe)
+    sd = make_state_dict(encoder, seed=0, num_frames=num_frames, pe=pe)
     ref_sd = m.state_dict()
-    spec = param_spec(encoder, num_frames)
+    spec = param_spec(encoder, num_frames, pe)
     assert list(ref_sd.keys()) == list(spec.keys()), "param_spec order/keys differ from the reference"
     for k, v in ref_sd.items():
         assert tuple(v.shape) == tuple(spec[k]), (k, v.shape, spec[k])
-    with open(os.path.join(GOLD, f"state_dict_keys_{encoder}.json"), "w") as f:
-        json.dump({k: list(v) for k, v in spec.items()}, f, indent=0)
+    if pe == "ape" and num_frames == 32:
+        with open(os.path.join(GOLD, f"state_dict_keys_{encoder}.json"), "w") as f:
+            json.dump({k: list(v) for k, v in spec.items()}, f, indent=0)
     # the recipe's pe buffer must equal the reference's own buffer
     for k, v in ref_sd.items():
         if k.endswith(".pe"):
@@ -73,8 +74,8 @@ def hook_taps(m):
     return got, hs
 
 
-def forward_case(name, encoder, T, H, W, seed, sub=1, skip_tmp_block=False):
-    m, sd = ref_model(encoder)
+def forward_case(name, encoder, T, H, W, seed, sub=1, skip_tmp_block=False, pe="ape"):
+    m, sd = ref_model(encoder, pe=pe)
     x = synthetic_clip(1, T, H, W, seed)
     got, hs = hook_taps(m)
     with torch.no_grad():
@@ -102,7 +103,7 @@ def forward_case(name, encoder, T, H, W, seed, sub=1, skip_tmp_block=False):
         t = feats[i][0]
         out[f"tap{i}"] = t[:, :: max(1, t.shape[1] // 64), :: max(1, t.shape[2] // 48)].numpy().astype(np.float32)
     np.savez_compressed(os.path.join(GOLD, f"forward_{name}.npz"), **out)
-    manifest["cases"][f"forward_{name}"] = {"encoder": encoder, "T": T, "H": H, "W": W, "seed": seed, "sub": sub,
+    manifest["cases"][f"forward_{name}"] = {"encoder": encoder, "T": T, "H": H, "W": W, "seed": seed, "sub": sub, "pe": pe,
                                             "oracle_vs_reference_max_abs": err,
                                             "depth_min": float(ref.min()), "depth_max": float(ref.max())}
 
@@ -146,7 +147,20 @@ def preprocess_case():
     return res
 
 
+def main_new_only():
+    """`make_goldens.py --new`: only the cases added after the first golden set (merged into MANIFEST.json)."""
+    with open(os.path.join(GOLD, "MANIFEST.json")) as f:
+        old = json.load(f)
+    forward_case("vits_T8_42x56_rope", "vits", 8, 42, 56, seed=7, pe="rope")
+    old["cases"].update(manifest["cases"])
+    with open(os.path.join(GOLD, "MANIFEST.json"), "w") as f:
+        json.dump(old, f, indent=1)
+
+
 if __name__ == "__main__":
+    if "--new" in sys.argv:
+        main_new_only()
+        sys.exit(0)
     maps = {str(n): odrv.window_index_map(n).tolist() for n in (1, 5, 22, 23, 32, 44, 45, 70, 100)}
     # pin the index map against the reference driver by feeding frames whose value encodes their index
     for n in (1, 23, 70):
@@ -171,6 +185,7 @@ if __name__ == "__main__":
     forward_case("vits_T32_28x28_skip", "vits", 32, 28, 28, seed=2, skip_tmp_block=True)
     forward_case("vits_T2_518x518", "vits", 2, 518, 518, seed=3, sub=7)
     forward_case("vitl_T3_28x42", "vitl", 3, 28, 42, seed=4)
+    forward_case("vits_T8_42x56_rope", "vits", 8, 42, 56, seed=7, pe="rope")
     driver_case("vits_n50_48x64", "vits", 50, 48, 64, 56, seed=5)
     driver_case("vits_n23_40x90", "vits", 23, 40, 90, 56, seed=6)  # ratio > 1.78 branch
     with open(os.path.join(GOLD, "MANIFEST.json"), "w") as f:

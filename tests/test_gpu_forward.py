@@ -22,14 +22,14 @@ dev = "cuda"
 _models = {}
 
 
-def get_model(enc):
+def get_model(enc, pe="ape"):
     from video_depth_anything_b200.video_depth import VideoDepthAnything
-    if enc not in _models:
-        m = VideoDepthAnything(**MODEL_CONFIGS[enc])
-        sd = make_state_dict(enc)
+    if (enc, pe) not in _models:
+        m = VideoDepthAnything(**MODEL_CONFIGS[enc], pe=pe)
+        sd = make_state_dict(enc, pe=pe)
         m.load_state_dict(sd, strict=True)
-        _models[enc] = (m.to(dev).eval(), {k: v.to(dev) for k, v in sd.items()})
-    return _models[enc]
+        _models[(enc, pe)] = (m.to(dev).eval(), {k: v.to(dev) for k, v in sd.items()})
+    return _models[(enc, pe)]
 
 
 def oracle_fp32(sd, x, enc, skip=False):
@@ -48,12 +48,13 @@ def oracle_bf16(sd, x, enc, skip=False):
         return omodel.forward(sd, x, enc, skip)
 
 
-@pytest.mark.parametrize("case", ["vits_T4_42x56", "vits_T32_28x28_skip", "vitl_T3_28x42", "vits_T2_518x518"])
+@pytest.mark.parametrize("case", ["vits_T4_42x56", "vits_T32_28x28_skip", "vitl_T3_28x42", "vits_T2_518x518",
+                                  "vits_T8_42x56_rope"])
 def test_fp32_build_matches_reference_golden(case):
     g = np.load(os.path.join(GOLD, f"forward_{case}.npz"))
     T, H, W, seed, sub, skip = [int(v) for v in g["meta"]]
     enc = "vitl" if case.startswith("vitl") else "vits"
-    m, sd = get_model(enc)
+    m, sd = get_model(enc, "rope" if case.endswith("rope") else "ape")
     x = synthetic_clip(1, T, H, W, seed).to(dev)
     with torch.no_grad():
         d = m(x, bool(skip))
@@ -88,6 +89,17 @@ def test_bf16_build_matches_autocast_oracle(enc, T, H, W, mode):
     assert ref.dtype == torch.float32
     f32 = oracle_fp32(sd, x, enc)
     bf16_gate(f"bf16 {enc} T{T} {H}x{W} {mode}", d.float(), ref.float(), f32)
+
+
+@pytest.mark.parametrize("enc,T,H,W", [("vits", 32, 70, 98), ("vitl", 8, 56, 84)])
+def test_bf16_build_rope_matches_autocast_oracle(enc, T, H, W):
+    """pe='rope' (SURVEY section 8f rank 3): q/k rotated by vda_rope_qk between the fused qkv GEMM and the attention."""
+    m, sd = get_model(enc, "rope")
+    x = synthetic_clip(1, T, H, W, 23).to(dev)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        d = m(x)
+    ref, f32 = oracle_bf16(sd, x, enc), oracle_fp32(sd, x, enc)
+    bf16_gate(f"bf16 rope {enc} T{T} {H}x{W}", d.float(), ref.float(), f32)
 
 
 def test_intermediate_taps_fp32():

@@ -327,3 +327,34 @@ def test_driver_kernels():
                                                                for f in post.cpu().numpy()]))
     L.check(lib.vda_blend(pre.data_ptr(), post.data_ptr(), stt.data_ptr(), 8, 60, st), "blend")
     assert np.abs(pre.cpu().numpy() - refb).max() < 1e-6
+
+
+@pytest.mark.parametrize("mode", ["f32", "bf16"])
+def test_rope_qk(mode):
+    """vda_rope_qk against `apply_rotary_emb` restated with torch complex arithmetic (motion_module/attention.py:419-429)."""
+    from oracle.model import rope_freqs_cis, rope_rotate
+    from video_depth_anything_b200.engine import _rope_table
+    L, lib = _lib()
+    torch.manual_seed(3)
+    b, T, hw, Cc = 2, 8, 37, 64
+    rows = b * T * hw
+    qkv = torch.randn(rows, 3 * Cc, device=dev)
+    dt = torch.bfloat16 if mode == "bf16" else torch.float32
+    buf = qkv.to(dt).contiguous()
+    src = buf.clone()
+    tab = _rope_table(Cc, 32, dev)
+    L.check(lib.vda_rope_qk(buf.data_ptr(), L.dt(buf), tab.data_ptr(), rows, hw, T, Cc, int(mode == "bf16"), L.stream_ptr()),
+            "vda_rope_qk")
+    torch.cuda.synchronize()
+    fc = rope_freqs_cis(Cc, 32)[:T].to(dev)
+    # rows are ((b, t), p): bring q / k to the reference's [(b p), t, c] view, rotate, and back
+    def ref_rot(x):
+        y = x.reshape(b, T, hw, Cc).permute(0, 2, 1, 3).reshape(b * hw, T, Cc)
+        y = rope_rotate(y, fc)
+        return y.reshape(b, hw, T, Cc).permute(0, 2, 1, 3).reshape(rows, Cc)
+    ref = torch.cat([ref_rot(src[:, :Cc]), ref_rot(src[:, Cc:2 * Cc]), src[:, 2 * Cc:]], 1)
+    assert torch.equal(buf[:, 2 * Cc:], src[:, 2 * Cc:])  # v is untouched
+    if mode == "bf16":
+        bf16_close("rope_bf16", buf.float(), ref.float(), ulps=1.0, frac=1e-3)
+    else:
+        assert stats("rope_f32", buf, ref)["max_rel_to_peak"] < 1e-6

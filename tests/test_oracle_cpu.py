@@ -51,12 +51,28 @@ def test_product_module_has_reference_state_dict(enc):
     assert torch.equal(pe, sinusoidal_pe(32, pe.shape[-1]))
 
 
-@pytest.mark.parametrize("case", ["vits_T4_42x56", "vits_T32_28x28_skip", "vitl_T3_28x42", "vits_T2_518x518"])
+def test_rope_model_has_no_pe_buffers():
+    """pe='rope' (video_depth.py:44 -> motion_module.py:238-242): freqs_cis is an attribute, not a buffer, so the state
+    dict is the 'ape' one minus the 8 `pos_encoder.pe` entries; the drop-in loads it with strict=True."""
+    from oracle.weights import MODEL_CONFIGS
+    from video_depth_anything_b200.video_depth import VideoDepthAnything
+
+    spec = param_spec("vits", pe="rope")
+    assert len(spec) == 351 - 8 and not any(k.endswith(".pe") for k in spec)
+    m = VideoDepthAnything(**MODEL_CONFIGS["vits"], pe="rope")
+    assert list(m.state_dict().keys()) == list(spec.keys())
+    m.load_state_dict(make_state_dict("vits", pe="rope"), strict=True)
+    with pytest.raises(NotImplementedError):
+        VideoDepthAnything(**MODEL_CONFIGS["vits"], pe="alibi")
+
+
+@pytest.mark.parametrize("case", ["vits_T4_42x56", "vits_T32_28x28_skip", "vitl_T3_28x42", "vits_T2_518x518",
+                                  "vits_T8_42x56_rope"])
 def test_oracle_forward_matches_reference_golden(case):
     g = _load(f"forward_{case}.npz")
     T, H, W, seed, sub, skip = [int(v) for v in g["meta"]]
     enc = "vitl" if case.startswith("vitl") else "vits"
-    sd = make_state_dict(enc)
+    sd = make_state_dict(enc, pe="rope" if case.endswith("rope") else "ape")
     x = synthetic_clip(1, T, H, W, seed)
     col = {}
     with torch.no_grad():

@@ -354,6 +354,54 @@ extern "C" int vda_attention(const void* qkv, void* o, int32_t dtype, int32_t fr
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Rotary position embedding of the temporal attention (pe='rope': motion_module/attention.py:403-429 applied at
+// motion_module.py:290-293).  The reference rotates the full C-wide q and k rows BEFORE the head split: consecutive
+// channel pairs (2i, 2i+1) are one complex number multiplied by exp(i t theta_i), theta_i = 10000^(-2i/C), t = frame
+// index, in fp32, then cast back to the activation type.  q and k live in columns [0, 2C) of the fused qkv matrix and
+// are rotated in place; tab[t, 2i .. 2i+1] = (cos, sin)(t theta_i) is the caller's copy of `freqs_cis`.
+template <typename T, bool RB>
+__global__ void rope_qk_kernel(T* __restrict__ qkv, const float* __restrict__ tab, long long rows, int hw, int Tn, int C) {
+  const int vpr = (2 * C) >> 3;  // 8-element vectors per row over the q and k columns
+  const long long total = rows * vpr;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / vpr;
+    const int c = (int)(i - r * vpr) << 3;   // column in [0, 2C)
+    const int cc = c >= C ? c - C : c;       // channel inside q or k
+    const int t = (int)((r / hw) % Tn);
+    T* p = qkv + r * (3LL * C) + c;
+    float v[8], w[8];
+    Vec8<T>::load(p, v);
+    const float4 a = *reinterpret_cast<const float4*>(tab + (long long)t * C + cc);
+    const float4 b = *reinterpret_cast<const float4*>(tab + (long long)t * C + cc + 4);
+    const float cs[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int k = 0; k < 8; k += 2) {
+      w[k] = R<RB>(v[k] * cs[k] - v[k + 1] * cs[k + 1]);
+      w[k + 1] = R<RB>(v[k] * cs[k + 1] + v[k + 1] * cs[k]);
+    }
+    Vec8<T>::store(p, w);
+  }
+}
+
+extern "C" int vda_rope_qk(void* qkv, int32_t dtype, const float* tab, int64_t rows, int32_t hw, int32_t T, int32_t C,
+                           int32_t round_bf16, vda_stream_t stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  VDA_CHECK_ARG(C % 8 == 0 && hw > 0 && T > 0, "vda_rope_qk: C must be a multiple of 8");
+  const bool bf = dtype == VDA_BF16 && round_bf16, f32 = dtype == VDA_F32 && !round_bf16;
+  VDA_CHECK_ARG(bf || f32, "vda_rope_qk: unsupported dtype/rounding combination");
+  if (rows == 0) return 0;
+  const long long total = rows * ((2LL * C) >> 3);
+  const int threads = 256;
+  long long want = (total + threads - 1) / threads;
+  const long long cap = (long long)vda_sm_count() * 16;
+  const int blocks = (int)(want < cap ? want : cap);
+  if (bf) rope_qk_kernel<bf16, true><<<blocks, threads, 0, st>>>(reinterpret_cast<bf16*>(qkv), tab, rows, hw, T, C);
+  else rope_qk_kernel<float, false><<<blocks, threads, 0, st>>>(reinterpret_cast<float*>(qkv), tab, rows, hw, T, C);
+  VDA_CUDA_LAUNCH_CHECK("rope_qk_kernel");
+  return 0;
+}
+
 extern "C" int vda_temporal_attention(const void* qkv, void* o, int32_t dtype, int32_t batch, int32_t T, int32_t hw,
                                       int32_t C, int32_t heads, int32_t round_bf16, vda_stream_t stream) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

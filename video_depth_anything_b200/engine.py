@@ -34,6 +34,15 @@ def _convt_pack(w: torch.Tensor) -> torch.Tensor:
     return w.permute(2, 3, 1, 0).reshape(k * k * co, ci).contiguous()
 
 
+def _rope_table(C_: int, max_len: int, device) -> torch.Tensor:
+    """`precompute_freqs_cis(query_dim, temporal_max_len)` (motion_module/attention.py:403-408) as interleaved
+    (cos, sin) fp32 pairs [max_len, C] -- the operand of vda_rope_qk."""
+    freqs = 1.0 / (10000.0 ** (torch.arange(0, C_, 2)[: (C_ // 2)].float() / C_))
+    ang = torch.outer(torch.arange(max_len, dtype=torch.float32), freqs)
+    cis = torch.polar(torch.ones_like(ang), ang)
+    return torch.view_as_real(cis).reshape(max_len, C_).contiguous().to(device)
+
+
 def _geglu_interleave(t: torch.Tensor) -> torch.Tensor:
     """Rows [value(4C) ; gate(4C)] -> groups of 64 rows = 32 value rows followed by their 32 gate rows."""
     half = t.shape[0] // 2
@@ -113,8 +122,13 @@ class PackedWeights:
         vec("oc2.b", sd[sc + "output_conv2.0.bias"])
         vec("oc2.hw", sd[sc + "output_conv2.2.weight"].reshape(32))
         self.head_b = float(sd[sc + "output_conv2.2.bias"].reshape(()).item())
+        # pe='rope' models carry no pos_encoder buffers (motion_module.py:226-240); the table length is num_frames
+        self.rope = getattr(model, "pe", "ape") == "rope"
+        pe_key = f"{h}motion_modules.0.temporal_transformer.transformer_blocks.0.attention_blocks.0.pos_encoder.pe"
+        self.pe_len = int(model.num_frames) if self.rope else int(sd[pe_key].shape[1])
         for m in range(4):
             t = f"{h}motion_modules.{m}.temporal_transformer."
+            C_m = int(sd[t + "norm.weight"].shape[0])
             vec(f"mm{m}.gn.w", sd[t + "norm.weight"])
             vec(f"mm{m}.gn.b", sd[t + "norm.bias"])
             mat(f"mm{m}.in.w", sd[t + "proj_in.weight"])
@@ -125,7 +139,10 @@ class PackedWeights:
                 mat(f"mm{m}.a{a}.qkv.w", torch.cat([sd[ab + "to_q.weight"], sd[ab + "to_k.weight"], sd[ab + "to_v.weight"]], 0))
                 mat(f"mm{m}.a{a}.out.w", sd[ab + "to_out.0.weight"])
                 vec(f"mm{m}.a{a}.out.b", sd[ab + "to_out.0.bias"])
-                vec(f"mm{m}.a{a}.pe", sd[ab + "pos_encoder.pe"][0])
+                if self.rope:
+                    w[f"mm{m}.a{a}.rope"] = _rope_table(C_m, self.pe_len, device)
+                else:
+                    vec(f"mm{m}.a{a}.pe", sd[ab + "pos_encoder.pe"][0])
                 vec(f"mm{m}.a{a}.ln.w", sd[f"{tb}norms.{a}.weight"])
                 vec(f"mm{m}.a{a}.ln.b", sd[f"{tb}norms.{a}.bias"])
             mat(f"mm{m}.ff1.w", _geglu_interleave(sd[tb + "ff.net.0.proj.weight"]))
@@ -137,7 +154,6 @@ class PackedWeights:
             mat(f"mm{m}.po.w", sd[t + "proj_out.weight"])
             vec(f"mm{m}.po.b", sd[t + "proj_out.bias"])
         self.w = w
-        self.pe_len = int(sd[f"{h}motion_modules.0.temporal_transformer.transformer_blocks.0.attention_blocks.0.pos_encoder.pe"].shape[1])
 
 
 class ForwardPlan:
@@ -313,9 +329,15 @@ class ForwardPlan:
                 W_[n + ".gn.b"].data_ptr(), 1e-6, self.BT, hw, C, 32, stats.data_ptr(), launches=3)
         self.gemm(g, W_[n + ".in.w"], M, C, C, bias=W_[n + ".in.b"], out=hbuf)
         for a in (0, 1):
-            self.layernorm(hbuf, nbuf, W_[f"{n}.a{a}.ln.w"], W_[f"{n}.a{a}.ln.b"], 1e-5, M, C, pe=W_[f"{n}.a{a}.pe"],
-                           pe_group=hw, pe_T=self.T)
+            if pw.rope:
+                self.layernorm(hbuf, nbuf, W_[f"{n}.a{a}.ln.w"], W_[f"{n}.a{a}.ln.b"], 1e-5, M, C)
+            else:
+                self.layernorm(hbuf, nbuf, W_[f"{n}.a{a}.ln.w"], W_[f"{n}.a{a}.ln.b"], 1e-5, M, C, pe=W_[f"{n}.a{a}.pe"],
+                               pe_group=hw, pe_T=self.T)
             self.gemm(nbuf, W_[f"{n}.a{a}.qkv.w"], M, 3 * C, C, out=qkv)
+            if pw.rope:  # rotate q and k in place (motion_module.py:290-293)
+                self.op(lib.vda_rope_qk, qkv.data_ptr(), self.dcode, W_[f"{n}.a{a}.rope"].data_ptr(), M, hw, self.T, C,
+                        int(self.bf16))
             self.op(lib.vda_temporal_attention, qkv.data_ptr(), att.data_ptr(), self.dcode, self.batch, self.T, hw, C, 8,
                     int(self.bf16))
             self.gemm(att, W_[f"{n}.a{a}.out.w"], M, C, C, bias=W_[f"{n}.a{a}.out.b"], out=hbuf, res=hbuf)

@@ -128,13 +128,17 @@ class _PosEnc(nn.Module):
 
 
 class _TemporalAttention(nn.Module):
-    def __init__(self, dim, max_len):
+    def __init__(self, dim, max_len, pe="ape"):
         super().__init__()
         self.to_q = nn.Linear(dim, dim, bias=False)
         self.to_k = nn.Linear(dim, dim, bias=False)
         self.to_v = nn.Linear(dim, dim, bias=False)
         self.to_out = nn.ModuleList([nn.Linear(dim, dim), nn.Dropout(0.0)])
-        self.pos_encoder = _PosEnc(dim, max_len)
+        # 'ape': a `pe` buffer in the state dict; 'rope': freqs_cis is a plain attribute, no state-dict entry
+        # (motion_module.py:226-240)
+        self.pos_embedding_type = pe
+        self.temporal_max_len = max_len
+        self.pos_encoder = _PosEnc(dim, max_len) if pe == "ape" else None
 
 
 class _GEGLU(nn.Module):
@@ -150,35 +154,35 @@ class _FeedForward(nn.Module):
 
 
 class _TemporalBlock(nn.Module):
-    def __init__(self, dim, max_len):
+    def __init__(self, dim, max_len, pe="ape"):
         super().__init__()
-        self.attention_blocks = nn.ModuleList([_TemporalAttention(dim, max_len) for _ in range(2)])
+        self.attention_blocks = nn.ModuleList([_TemporalAttention(dim, max_len, pe) for _ in range(2)])
         self.norms = nn.ModuleList([nn.LayerNorm(dim) for _ in range(2)])
         self.ff = _FeedForward(dim)
         self.ff_norm = nn.LayerNorm(dim)
 
 
 class _TemporalTransformer(nn.Module):
-    def __init__(self, C, max_len):
+    def __init__(self, C, max_len, pe="ape"):
         super().__init__()
         self.norm = nn.GroupNorm(32, C, eps=1e-6, affine=True)
         self.proj_in = nn.Linear(C, C)
-        self.transformer_blocks = nn.ModuleList([_TemporalBlock(C, max_len)])
+        self.transformer_blocks = nn.ModuleList([_TemporalBlock(C, max_len, pe)])
         self.proj_out = nn.Linear(C, C)
         for p in self.proj_out.parameters():  # zero_module, motion_module.py:61-62
             p.detach().zero_()
 
 
 class TemporalModuleParams(nn.Module):
-    def __init__(self, C, max_len):
+    def __init__(self, C, max_len, pe="ape"):
         super().__init__()
-        self.temporal_transformer = _TemporalTransformer(C, max_len)
+        self.temporal_transformer = _TemporalTransformer(C, max_len, pe)
 
 
 class DPTHeadTemporalParams(nn.Module):
     """`DPTHeadTemporal` parameter tree (use_bn=False, use_clstoken=False: the only configuration any caller uses)."""
 
-    def __init__(self, in_channels, features, out_channels, num_frames):
+    def __init__(self, in_channels, features, out_channels, num_frames, pe="ape"):
         super().__init__()
         oc = out_channels
         self.projects = nn.ModuleList([nn.Conv2d(in_channels, c, 1, 1, 0) for c in oc])
@@ -190,5 +194,5 @@ class DPTHeadTemporalParams(nn.Module):
         ])
         self.scratch = _Scratch(oc, features)
         self.motion_modules = nn.ModuleList(
-            [TemporalModuleParams(c, num_frames) for c in (oc[2], oc[3], features, features)]
+            [TemporalModuleParams(c, num_frames, pe) for c in (oc[2], oc[3], features, features)]
         )

@@ -32,15 +32,16 @@ class VideoDepthAnything(nn.Module):
         super().__init__()
         if use_bn or use_clstoken:
             raise NotImplementedError("use_bn / use_clstoken are never enabled by the reference's callers (run.py:74-77)")
-        if pe != "ape":
-            raise NotImplementedError("only pe='ape' (the reference default, video_depth.py:44) is implemented")
+        if pe not in ("ape", "rope"):
+            raise NotImplementedError(pe)  # motion_module.py:242-243
         self.intermediate_layer_idx = {"vits": [2, 5, 8, 11], "vitl": [4, 11, 17, 23]}
         if encoder not in self.intermediate_layer_idx:
             raise KeyError(encoder)
         self.encoder = encoder
         self.num_frames = num_frames
+        self.pe = pe
         self.pretrained = DinoV2Params(encoder)
-        self.head = DPTHeadTemporalParams(self.pretrained.embed_dim, features, list(out_channels), num_frames)
+        self.head = DPTHeadTemporalParams(self.pretrained.embed_dim, features, list(out_channels), num_frames, pe)
         self._packed = {}   # (device, bf16) -> (version key, PackedWeights)
         self._plans = {}    # (device, bf16, B, T, H, W, skip) -> ForwardPlan
         self.force_simt = False  # tests: run the bf16 build on the SIMT kernels instead of tcgen05
