@@ -203,6 +203,17 @@ int vda_scale_shift(const float* pred, const float* target, int64_t count, doubl
 /* out = max(in*st[0] + st[1], 0) over count elements (video_depth.py:399-412). */
 int vda_scale_clamp(const float* in, float* out, const float* st, int64_t count, vda_stream_t stream);
 
+/* out = in*st[0] + st[1] over count elements, not clamped: the per-frame alignment of the streaming mode
+ * (`infere_single_image`, video_depth.py:310-315). */
+int vda_scale_apply(const float* in, float* out, const float* st, int64_t count, vda_stream_t stream);
+
+/* Frame gather / scatter of the streaming mode's feature store (video_depth.py:228-231,244-258,281-296; the `torch.cat`
+ * of stored and new features at dpt_temporal.py:188-196 and the prediction subset at :222-227):
+ * frame dst_idx[i] of dst <- frame src_idx[i] of src for i < n; a NULL index array means i.  Index arrays are DEVICE
+ * int32 arrays so the launch is static under a CUDA graph.  frame_bytes must be a multiple of 16. */
+int vda_copy_frames(const void* src, void* dst, const int32_t* src_idx, const int32_t* dst_idx, int32_t n,
+                    int64_t frame_bytes, vda_stream_t stream);
+
 /* 8-frame linear cross-fade (utils/util.py:65-74, video_depth.py:397-402):
  * inout[i] = inout[i]*(1-w_i) + max(post[i]*st[0]+st[1], 0)*w_i, w = i/(n-1). */
 int vda_blend(float* inout, const float* post, const float* st, int32_t n, int64_t frame_elems, vda_stream_t stream);

@@ -185,3 +185,97 @@ def infer_video_depth(frames, target_fps, forward_fn, input_size=518, device="cp
     if return_raw:
         return out, target_fps, depth_list, st
     return out, target_fps
+
+
+# --------------------------------------------------------------------------- streaming mode
+def stream_schedule(inference_length: int, keyframe_list):
+    """The index bookkeeping of `infere_single_image`, video_depth.py:139-185: for each of the first max(keyframes)+1
+    predicting steps, the rows of the feature store that form the T-1 context frames (`use_feature_idx`) and the
+    positions inside that context used for alignment (`Align_idx`); afterwards the last entry is used for good and the
+    store itself is shifted.  Quirks kept: row indices of keyframes that do not exist yet point at still-zero rows."""
+    L, nk, max_kf = inference_length, len(keyframe_list), max(keyframe_list)
+    dist = [kf + (L - nk) for kf in keyframe_list]
+    static = [L - kf if L > kf else i + 1 for i, kf in enumerate(keyframe_list)]
+    assert len(static) == len(set(static)), f"Setup leads to duplicates in the keyframes: {static}"
+    use, align = [], []
+    for fi in range(L - 1, L + max_kf):
+        rows = list(range(fi - (L - 1), fi))
+        rows[0] = 0  # the first frame is always the reference
+        al = [0]
+        for i, sk in enumerate(static):
+            if sk in rows:
+                al.append(rows.index(sk))
+            else:
+                al.append(i + 1)
+                rows[i + 1] = sk if fi - dist[i] <= sk else fi - dist[i]
+        use.append(rows)
+        align.append(al)
+    return use, align
+
+
+def infere_single_image(frames, target_fps, step_fn, reassemble_fn, input_size=518, device="cpu", fp32=True,
+                        inference_length=32, keyframe_list=(0, 12), align_each_new_frame=True, autocast_dtype=None):
+    """`VideoDepthAnything.infere_single_image` (warmup=True), video_depth.py:93-327, with the network as parameters:
+    reassemble_fn(x[1,1,3,h,w]) -> (layer_1..4) of one frame (encoder + `get_motion_features`);
+    step_fn(x, motion_features, pred_depth_idx) -> (depth [1,n,h,w], (layer_1..4 of the new frame))."""
+    import torch
+    import torch.nn.functional as F
+
+    keyframe_list = list(keyframe_list)
+    L, max_kf = inference_length, max(keyframe_list)
+    n = frames.shape[0]
+    fh, fw = frames[0].shape[:2]
+    input_size = effective_input_size(fh, fw, input_size)
+    use, align = stream_schedule(L, keyframe_list)
+    R = L + max_kf - 1
+    move = [i for i in range(R) if i != 1]
+    dev_type = torch.device(device).type
+
+    def net(fn, *a):
+        with torch.no_grad():
+            if fp32:
+                return fn(*a)
+            with torch.autocast(device_type=dev_type, dtype=autocast_dtype):
+                return fn(*a)
+
+    store = None
+    depth_list = []
+    first = True
+    for i in range(n):
+        cur = torch.from_numpy(preprocess_frame(frames[i], input_size))[None, None].to(device)
+        if i < L - 1:
+            feats = net(reassemble_fn, cur)
+            if store is None:
+                store = [torch.zeros(R, *f.shape[1:]).to(device) for f in feats]
+            for s_, f in zip(store, feats):
+                s_[i] = f[0]
+            continue
+        k = min(i - (L - 1), len(use) - 1)
+        rows = use[k]
+        pred_idx = abs_idx = None
+        if align_each_new_frame:
+            pred_idx = rows if i == L - 1 else align[k]
+            abs_idx = [rows[t] for t in align[k]]
+            if i >= L + max_kf:  # the store has been shifted i - (L + max_kf) + 1 times; row 0 never moves
+                abs_idx = [0 if a == 0 else a + (i - (L + max_kf)) + 1 for a in abs_idx]
+        depth, new = net(step_fn, cur, tuple(s_[rows] for s_ in store), pred_idx)
+        for s_, f in zip(store, new):
+            if i < R:
+                s_[i] = f[0]
+            else:
+                s_[:-1] = s_[move]
+                s_[-1] = f[0]
+        depth = depth.to(cur.dtype)
+        depth = F.interpolate(depth.flatten(0, 1).unsqueeze(1), size=(fh, fw), mode="bilinear", align_corners=True)
+        maps = [depth[j][0].cpu().numpy() for j in range(depth.shape[0])]
+        if not align_each_new_frame or first:
+            depth_list += maps
+            first = False
+        else:
+            old = [depth_list[j] for j in abs_idx]
+            scale, shift = compute_scale_and_shift(np.concatenate(maps[:len(pred_idx)]), np.concatenate(old),
+                                                   np.concatenate(np.ones_like(old) == 1))
+            depth_list.append(maps[-1] * scale + shift)
+    if align_each_new_frame:
+        return np.stack(depth_list[1:n], axis=0), target_fps  # the first frame only serves the alignment
+    return np.stack(depth_list[:n], axis=0), target_fps

@@ -185,6 +185,79 @@ def _fusion(sd, p: str, x0: torch.Tensor, x1, size) -> torch.Tensor:
     return F.conv2d(out, sd[p + "out_conv.weight"], sd[p + "out_conv.bias"])
 
 
+def reassemble(sd, taps, ph: int, pw: int):
+    """projects + resize_layers: `DPTHeadTemporal.get_motion_features`, dpt_temporal.py:101-130 (== :55-69)."""
+    h = "head."
+    layers = []
+    for i, x in enumerate(taps):
+        BT, _, D = x.shape
+        x = x.permute(0, 2, 1).reshape(BT, D, ph, pw)
+        x = F.conv2d(x, sd[f"{h}projects.{i}.weight"], sd[f"{h}projects.{i}.bias"])
+        if i == 0:
+            x = F.conv_transpose2d(x, sd[h + "resize_layers.0.weight"], sd[h + "resize_layers.0.bias"], stride=4)
+        elif i == 1:
+            x = F.conv_transpose2d(x, sd[h + "resize_layers.1.weight"], sd[h + "resize_layers.1.bias"], stride=2)
+        elif i == 3:
+            x = F.conv2d(x, sd[h + "resize_layers.3.weight"], sd[h + "resize_layers.3.bias"], stride=2, padding=1)
+        layers.append(x)
+    return layers
+
+
+def _output_convs(sd, p1: torch.Tensor, ph: int, pw: int) -> torch.Tensor:
+    """output_conv1 -> bilinear -> fp32 island output_conv2 (dpt_temporal.py:91-99 == :230-240,249-258)."""
+    sc = "head.scratch."
+    out = F.conv2d(p1, sd[sc + "output_conv1.weight"], sd[sc + "output_conv1.bias"], padding=1)
+    out = F.interpolate(out, (ph * PATCH, pw * PATCH), mode="bilinear", align_corners=True)
+    ori = out.dtype
+    with torch.autocast(device_type="cuda", enabled=False):
+        o = F.conv2d(out.float(), sd[sc + "output_conv2.0.weight"], sd[sc + "output_conv2.0.bias"], padding=1)
+        o = F.relu(o)
+        o = F.conv2d(o, sd[sc + "output_conv2.2.weight"], sd[sc + "output_conv2.2.bias"])
+        o = F.relu(o)
+    return o.to(ori)
+
+
+def head_single_image(sd, taps, ph: int, pw: int, T: int, motion_features, pred_depth_idx=None,
+                      skip_tmp_block: bool = False):
+    """`DPTHeadTemporal.foward_single_image`, dpt_temporal.py:132-260.  taps: the new frame's 4 encoder taps [1, N, D];
+    motion_features: stored (layer_1..4) of the T-1 context frames, NCHW.  Only the frames `pred_depth_idx` + the new
+    one go through refinenet2/1 and the output convs (the reference's chunks of `max_head_pred_length` frames are a
+    memory measure: every op of that part is per frame).  Returns (depth [n,1,H,W], layer_1..4 of the new frame)."""
+    h, sc = "head.", "head.scratch."
+    l1, l2, l3, l4 = reassemble(sd, taps, ph, pw)
+    o1, o2, o3, o4 = motion_features
+    if pred_depth_idx is not None:
+        l1p, l2p = torch.cat([o1[pred_depth_idx], l1], 0), torch.cat([o2[pred_depth_idx], l2], 0)
+    else:
+        l1p, l2p = l1, l2
+    l3c, l4c = torch.cat([o3, l3], 0), torch.cat([o4, l4], 0)
+    l1r = F.conv2d(l1p, sd[sc + "layer1_rn.weight"], None, padding=1)
+    l2r = F.conv2d(l2p, sd[sc + "layer2_rn.weight"], None, padding=1)
+    l4r = F.conv2d(temporal_module(sd, h + "motion_modules.1.", l4c, T), sd[sc + "layer4_rn.weight"], None, padding=1)
+    l3r = F.conv2d(temporal_module(sd, h + "motion_modules.0.", l3c, T), sd[sc + "layer3_rn.weight"], None, padding=1)
+    p4 = _fusion(sd, sc + "refinenet4.", l4r, None, l3r.shape[2:])
+    if not skip_tmp_block:
+        p4 = temporal_module(sd, h + "motion_modules.2.", p4, T)
+    p3 = _fusion(sd, sc + "refinenet3.", p4, l3r, l2r.shape[2:])
+    p3 = temporal_module(sd, h + "motion_modules.3.", p3, T)
+    p3 = p3[list(pred_depth_idx) + [p3.shape[0] - 1]] if pred_depth_idx is not None else p3[-1:]
+    p2 = _fusion(sd, sc + "refinenet2.", p3, l2r, l1r.shape[2:])
+    p1 = _fusion(sd, sc + "refinenet1.", p2, l1r, None)
+    return _output_convs(sd, p1, ph, pw), l1, l2, l3, l4
+
+
+def forward_single_image(sd, x: torch.Tensor, encoder: str, motion_features, pred_depth_idx=None, inference_length=32,
+                         skip_tmp_block: bool = False):
+    """`VideoDepthAnything.forward_single_image`, video_depth.py:67-91.  x [1,1,3,H,W]."""
+    B, T, _, H, W = x.shape
+    ph, pw = H // PATCH, W // PATCH
+    taps = encoder_taps(sd, x.flatten(0, 1), encoder)
+    d, l1, l2, l3, l4 = head_single_image(sd, taps, ph, pw, inference_length, motion_features, pred_depth_idx, skip_tmp_block)
+    d = F.relu(F.interpolate(d, size=(H, W), mode="bilinear", align_corners=True))
+    n = T if pred_depth_idx is None else len(pred_depth_idx) + 1
+    return d.squeeze(1).unflatten(0, (B, n)), (l1, l2, l3, l4)
+
+
 def head_forward(sd, taps, ph: int, pw: int, T: int, skip_tmp_block: bool = False, collect=None) -> torch.Tensor:
     """`DPTHeadTemporal.forward`, dpt_temporal.py:53-99 (layers built in dpt.py:47-124)."""
     h = "head."

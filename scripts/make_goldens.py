@@ -147,12 +147,52 @@ def preprocess_case():
     return res
 
 
+def stream_case(name, n, fh, fw, input_size, seed, **kw):
+    """Reference `infere_single_image` (CPU fp32) vs the oracle restatement; golden = the reference's output."""
+    m, sd = ref_model("vits")
+    frames = synthetic_video(n, fh, fw, seed)
+    ref, fps = m.infere_single_image(frames, 24, input_size=input_size, device="cpu", fp32=True, **kw)
+    T = kw.get("inference_length", 32)
+
+    def reas(x):
+        return omodel.reassemble(sd, omodel.encoder_taps(sd, x.flatten(0, 1), "vits"), x.shape[-2] // 14, x.shape[-1] // 14)
+
+    def step(x, mf, pi):
+        return omodel.forward_single_image(sd, x, "vits", mf, pi, T)
+
+    ora, _ = odrv.infere_single_image(frames, 24, step, reas, input_size=input_size, **kw)
+    err = float(np.abs(ora - ref).max())
+    print(f"{name}: stream oracle-vs-reference max|d| {err:.3e}; out {ref.shape} range [{ref.min():.4f},{ref.max():.4f}]")
+    assert ora.shape == ref.shape and err <= 1e-5 * float(np.abs(ref).max()) + 1e-6
+    np.savez_compressed(os.path.join(GOLD, f"stream_{name}.npz"), depth=ref.astype(np.float32),
+                        meta=np.array([n, fh, fw, input_size, seed, T, int(kw.get("align_each_new_frame", True))]
+                                      + list(kw["keyframe_list"]), dtype=np.int64))
+    manifest["cases"][f"stream_{name}"] = {"encoder": "vits", "n": n, "fh": fh, "fw": fw, "input_size": input_size,
+                                           "seed": seed, **kw, "oracle_vs_reference_max_abs": err}
+
+
+def stream_cases():
+    stream_case("vits_n40_T8_k25_align", 40, 40, 56, 42, seed=8, inference_length=8, keyframe_list=[2, 5])
+    stream_case("vits_n40_T8_k03_noalign", 40, 40, 56, 42, seed=8, inference_length=8, keyframe_list=[0, 3],
+                align_each_new_frame=False)
+    stream_case("vits_n50_T32_k212_align", 50, 28, 42, 28, seed=9, keyframe_list=[2, 12])
+    # the reference's own defaults (keyframe_list=[0, 12], align_each_new_frame=True) raise IndexError at the first prediction
+    m, _ = ref_model("vits")
+    try:
+        m.infere_single_image(synthetic_video(34, 28, 42, 9), 24, input_size=28, device="cpu", fp32=True)
+        raise SystemExit("the reference's default streaming call was expected to raise IndexError")
+    except IndexError as e:
+        manifest["stream_default_args_error"] = f"IndexError: {e}"
+
+
 def main_new_only():
     """`make_goldens.py --new`: only the cases added after the first golden set (merged into MANIFEST.json)."""
     with open(os.path.join(GOLD, "MANIFEST.json")) as f:
         old = json.load(f)
     forward_case("vits_T8_42x56_rope", "vits", 8, 42, 56, seed=7, pe="rope")
+    stream_cases()
     old["cases"].update(manifest["cases"])
+    old["stream_default_args_error"] = manifest["stream_default_args_error"]
     with open(os.path.join(GOLD, "MANIFEST.json"), "w") as f:
         json.dump(old, f, indent=1)
 
@@ -186,6 +226,7 @@ if __name__ == "__main__":
     forward_case("vits_T2_518x518", "vits", 2, 518, 518, seed=3, sub=7)
     forward_case("vitl_T3_28x42", "vitl", 3, 28, 42, seed=4)
     forward_case("vits_T8_42x56_rope", "vits", 8, 42, 56, seed=7, pe="rope")
+    stream_cases()
     driver_case("vits_n50_48x64", "vits", 50, 48, 64, 56, seed=5)
     driver_case("vits_n23_40x90", "vits", 23, 40, 90, 56, seed=6)  # ratio > 1.78 branch
     with open(os.path.join(GOLD, "MANIFEST.json"), "w") as f:

@@ -192,3 +192,79 @@ def test_driver_bf16_matches_autocast_oracle():
                                     fp32=False, autocast_dtype=torch.bfloat16)
     ref32, _ = odrv.infer_video_depth(frames, 24, lambda x: oracle_fp32(sd, x, "vits"), input_size=isz, device="cuda", fp32=True)
     bf16_gate("driver bf16", torch.from_numpy(out), torch.from_numpy(ref), torch.from_numpy(ref32))
+
+
+STREAM_CASES = ["vits_n40_T8_k25_align", "vits_n40_T8_k03_noalign", "vits_n50_T32_k212_align"]
+
+
+def _stream_meta(g):
+    n, fh, fw, isz, seed, T, align = [int(v) for v in g["meta"][:7]]
+    return n, fh, fw, isz, seed, T, bool(align), [int(v) for v in g["meta"][7:]]
+
+
+def _oracle_stream(sd, frames, isz, T, kf, align, fp32, fwd32=False):
+    def wrap(fn):
+        if not fwd32:
+            return fn
+        def g(*a):
+            old = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+            torch.backends.cuda.matmul.allow_tf32 = False
+            torch.backends.cudnn.allow_tf32 = False
+            try:
+                return fn(*a)
+            finally:
+                torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
+        return g
+
+    def reas(x):
+        return omodel.reassemble(sd, omodel.encoder_taps(sd, x.flatten(0, 1), "vits"), x.shape[-2] // 14, x.shape[-1] // 14)
+
+    def step(x, mf, pi):
+        return omodel.forward_single_image(sd, x, "vits", mf, pi, T)
+
+    return odrv.infere_single_image(frames, 24, wrap(step), wrap(reas), input_size=isz, device="cuda", fp32=fp32,
+                                    inference_length=T, keyframe_list=kf, align_each_new_frame=align,
+                                    autocast_dtype=torch.bfloat16)[0]
+
+
+@pytest.mark.parametrize("case", STREAM_CASES)
+def test_stream_fp32_matches_reference_golden(case):
+    """Streaming mode: `infere_single_image` fp32 build vs the real reference's output."""
+    g = np.load(os.path.join(GOLD, f"stream_{case}.npz"))
+    n, fh, fw, isz, seed, T, align, kf = _stream_meta(g)
+    m, sd = get_model("vits")
+    frames = synthetic_video(n, fh, fw, seed)
+    out, fps = m.infere_single_image(frames, 24, input_size=isz, device="cuda", fp32=True, inference_length=T,
+                                     keyframe_list=kf, align_each_new_frame=align)
+    assert fps == 24 and out.shape == g["depth"].shape and out.dtype == np.float32
+    e = rel_err_map(torch.from_numpy(out), torch.from_numpy(g["depth"]))
+    print(f"[stream {case}] max rel-err {e.max().item():.3e}")
+    assert e.max().item() <= 1e-3
+    out2, _ = m.infere_single_image(frames, 24, input_size=isz, device="cuda", fp32=True, inference_length=T,
+                                    keyframe_list=kf, align_each_new_frame=align)
+    assert np.array_equal(out, out2)  # second call: CUDA-graph replays of the stages, store re-zeroed
+
+
+@pytest.mark.parametrize("T,kf,align", [(8, [2, 5], True), (32, [0, 12], False)])
+def test_stream_bf16_matches_autocast_oracle(T, kf, align):
+    n, fh, fw, isz = 44, 56, 84, 56
+    m, sd = get_model("vits")
+    frames = synthetic_video(n, fh, fw, 11)
+    out, _ = m.infere_single_image(frames, 24, input_size=isz, device="cuda", fp32=False, inference_length=T,
+                                   keyframe_list=kf, align_each_new_frame=align)
+    ref = _oracle_stream(sd, frames, isz, T, kf, align, fp32=False)
+    ref32 = _oracle_stream(sd, frames, isz, T, kf, align, fp32=True, fwd32=True)
+    assert out.shape == ref.shape
+    bf16_gate(f"stream bf16 T{T} kf{kf} align{int(align)}", torch.from_numpy(out), torch.from_numpy(ref), torch.from_numpy(ref32))
+
+
+def test_stream_contract():
+    """Failure modes of the reference's streaming entry point (video_depth.py:321-327, dpt_temporal.py:188-189)."""
+    m, sd = get_model("vits")
+    frames = synthetic_video(34, 28, 42, 9)
+    with pytest.raises(IndexError):   # the reference's own defaults (keyframe_list=[0, 12], align) index past the context
+        m.infere_single_image(frames, 24, input_size=28, device="cuda", fp32=True)
+    with pytest.raises(NotImplementedError):
+        m.infere_single_image(frames, 24, input_size=28, device="cuda", fp32=True, warmup=False)
+    with pytest.raises(ValueError):   # fewer frames than the context: nothing to stack
+        m.infere_single_image(frames[:20], 24, input_size=28, device="cuda", fp32=True, align_each_new_frame=False)

@@ -99,6 +99,57 @@ def test_oracle_driver_matches_reference_golden(case):
     assert np.allclose(np.asarray(st), g["scale_shift"], rtol=1e-4, atol=1e-4)
 
 
+STREAM_CASES = ["vits_n40_T8_k25_align", "vits_n40_T8_k03_noalign", "vits_n50_T32_k212_align"]
+
+
+def stream_meta(g):
+    n, fh, fw, isz, seed, T, align = [int(v) for v in g["meta"][:7]]
+    return n, fh, fw, isz, seed, T, bool(align), [int(v) for v in g["meta"][7:]]
+
+
+@pytest.mark.parametrize("case", STREAM_CASES)
+def test_oracle_stream_matches_reference_golden(case):
+    """`infere_single_image` (video_depth.py:93-327): oracle restatement vs the real reference's output."""
+    g = _load(f"stream_{case}.npz")
+    n, fh, fw, isz, seed, T, align, kf = stream_meta(g)
+    sd = make_state_dict("vits")
+    frames = synthetic_video(n, fh, fw, seed)
+
+    def reas(x):
+        return omodel.reassemble(sd, omodel.encoder_taps(sd, x.flatten(0, 1), "vits"), x.shape[-2] // 14, x.shape[-1] // 14)
+
+    out, fps = odrv.infere_single_image(frames, 24, lambda x, mf, pi: omodel.forward_single_image(sd, x, "vits", mf, pi, T),
+                                        reas, input_size=isz, inference_length=T, keyframe_list=kf, align_each_new_frame=align)
+    assert fps == 24 and out.shape == g["depth"].shape == ((n - 1) if align else (n - T + 1), fh, fw)
+    assert np.abs(out - g["depth"]).max() <= 2e-5 * np.abs(g["depth"]).max()
+
+
+def test_stream_schedule_and_feature_store():
+    """Host logic of the streaming mode: the product's schedule equals the oracle's (pinned to the reference through the
+    goldens above), and the slot table reproduces the reference's shifting store (video_depth.py:281-296)."""
+    from video_depth_anything_b200 import stream as pstream
+
+    for T, kf in [(32, [0, 12]), (32, [2, 12]), (8, [2, 5]), (8, [0, 3]), (16, [3, 7, 20]), (8, [9, 3]), (32, [5, 40])]:
+        assert pstream.stream_schedule(T, kf) == odrv.stream_schedule(T, kf)
+    with pytest.raises(AssertionError):
+        pstream.stream_schedule(8, [3, 3])
+    ctx, pos = pstream.stream_schedule(32, [0, 12])
+    assert ctx[0][:3] == [0, 32, 2] and pos[0] == [0, 1, 20]  # the default key row 32 does not exist yet: IndexError upstream
+    rows = 11
+    store = pstream.FeatureStore(rows)
+    literal = [-1] * rows          # the reference's tensor, holding frame numbers
+    phys = [-1] * rows             # what each physical slot holds
+    move = [i for i in range(rows) if i != 1]
+    for i in range(40):
+        phys[store.write(i)] = i
+        if i < rows:
+            literal[i] = i
+        else:
+            literal[:-1] = [literal[j] for j in move]
+            literal[-1] = i
+        assert [phys[s] for s in store.slot] == literal
+
+
 def test_window_index_map_golden_and_product():
     from video_depth_anything_b200 import driver as pdrv
 

@@ -123,6 +123,26 @@ __global__ void __launch_bounds__(256) scale_clamp_kernel(const float* __restric
     out[i] = fmaxf(__fadd_rn(__fmul_rn(in[i], s), t), 0.f);
 }
 
+// streaming mode (video_depth.py:313): cur_prediction * scale + shift, NOT clamped
+__global__ void __launch_bounds__(256) scale_apply_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                         const float* __restrict__ st, long long count) {
+  const float s = st[0], t = st[1];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x)
+    out[i] = __fadd_rn(__fmul_rn(in[i], s), t);
+}
+
+// Frame gather / scatter for the streaming mode's feature ring (video_depth.py:228-231,244-247,281-296):
+// dst frame dst_idx[i] <- src frame src_idx[i]; frames are `vecs` 16-byte vectors; NULL index arrays mean i.
+__global__ void __launch_bounds__(256) copy_frames_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst,
+                                                         const int* __restrict__ src_idx, const int* __restrict__ dst_idx,
+                                                         long long vecs) {
+  const int f = blockIdx.y;
+  const uint4* a = src + (long long)(src_idx ? src_idx[f] : f) * vecs;
+  uint4* b = dst + (long long)(dst_idx ? dst_idx[f] : f) * vecs;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < vecs; i += (long long)gridDim.x * blockDim.x)
+    b[i] = a[i];
+}
+
 __global__ void __launch_bounds__(256) blend_kernel(float* __restrict__ inout, const float* __restrict__ post,
                                                    const float* __restrict__ st, int n, long long frame_elems) {
   const float s = st[0], t = st[1];
@@ -192,6 +212,33 @@ extern "C" int vda_scale_clamp(const float* in, float* out, const float* st, int
   if (blocks < 1) blocks = 1;
   scale_clamp_kernel<<<blocks, 256, 0, s>>>(in, out, st, count);
   VDA_CUDA_LAUNCH_CHECK("scale_clamp_kernel");
+  return 0;
+}
+
+extern "C" int vda_scale_apply(const float* in, float* out, const float* st, int64_t count, vda_stream_t stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  int blocks = (int)((count + 256 * 4 - 1) / (256 * 4));
+  if (blocks > 8 * vda_sm_count()) blocks = 8 * vda_sm_count();
+  if (blocks < 1) blocks = 1;
+  scale_apply_kernel<<<blocks, 256, 0, s>>>(in, out, st, count);
+  VDA_CUDA_LAUNCH_CHECK("scale_apply_kernel");
+  return 0;
+}
+
+extern "C" int vda_copy_frames(const void* src, void* dst, const int32_t* src_idx, const int32_t* dst_idx, int32_t n,
+                               int64_t frame_bytes, vda_stream_t stream) {
+  VDA_CHECK_ARG(frame_bytes % 16 == 0, "vda_copy_frames: frame_bytes must be a multiple of 16");
+  VDA_CHECK_ARG(((uintptr_t)src | (uintptr_t)dst) % 16 == 0, "vda_copy_frames: pointers must be 16-byte aligned");
+  if (n <= 0 || frame_bytes == 0) return 0;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const long long vecs = frame_bytes / 16;
+  long long bx = (vecs + 256 * 4 - 1) / (256 * 4);
+  const long long cap = (8LL * vda_sm_count() + n - 1) / n;
+  if (bx > cap) bx = cap;
+  if (bx < 1) bx = 1;
+  copy_frames_kernel<<<dim3((unsigned)bx, (unsigned)n), 256, 0, s>>>(reinterpret_cast<const uint4*>(src),
+                                                                   reinterpret_cast<uint4*>(dst), src_idx, dst_idx, vecs);
+  VDA_CUDA_LAUNCH_CHECK("copy_frames_kernel");
   return 0;
 }
 

@@ -184,19 +184,29 @@ class ForwardPlan:
         self.use_graph = os.environ.get("VDA_NO_GRAPH", "0") != "1"
         self._graph = None
         self._eager_runs = 0
+        self._prefix = ""   # name prefix of the buffers being built (stages that repeat a builder need distinct names)
+        self._alias = {}    # name -> caller-provided tensor to use instead of allocating (streaming mode's feature store)
         self._build(skip_tmp_block)
         if not self.use_tc:
             self._ws = torch.empty(max(self._ws_need, 4), dtype=torch.uint8, device=device)
-            for fn, args in self.ops:
+            for fn, args in self._all_ops():
                 if fn is self._lib.vda_gemm:
                     args[0].workspace = self._ws.data_ptr()
                     args[0].workspace_bytes = self._ws.numel()
 
+    def _all_ops(self):
+        return self.ops
+
     # ------------------------------------------------------------------ buffer helpers
     def buf(self, name, rows, cols, dtype=None, zero=False):
         dtype = dtype or self.adt
-        t = (torch.zeros if zero else torch.empty)((rows, cols), dtype=dtype, device=self.device)
-        self.bufs[name] = t
+        if name in self._alias:
+            t = self._alias.pop(name)
+            assert tuple(t.shape) == (rows, cols) and t.dtype == dtype and t.is_contiguous(), (name, t.shape, rows, cols)
+        else:
+            t = (torch.zeros if zero else torch.empty)((rows, cols), dtype=dtype, device=self.device)
+        assert self._prefix + name not in self.bufs, self._prefix + name  # a dropped reference would free a live buffer
+        self.bufs[self._prefix + name] = t
         return t
 
     def padded(self, name, h, w, C):
@@ -258,6 +268,10 @@ class ForwardPlan:
 
     # ------------------------------------------------------------------ the network
     def _build(self, skip_tmp_block):
+        self._build_head(self._build_encoder(), skip_tmp_block)
+
+    def _build_encoder(self):
+        """Patch embed + transformer blocks + the final norm on the four taps (dinov2.py:297-321).  Returns the taps."""
         pw, W_ = self.pw, self.pw.w
         BT, ph, pwid, D = self.BT, self.ph, self.pw_, pw.D
         P = ph * pwid
@@ -306,7 +320,7 @@ class ForwardPlan:
                 # final norm on the tap, class token dropped (dinov2.py:309-312)
                 self.layernorm(resid, t, W_["norm.w"], W_["norm.b"], 1e-6, M, D, group_rows=ntok, skip_first=1)
                 taps.append(t)
-        self._build_head(taps, skip_tmp_block)
+        return taps
 
     # ------------------------------------------------------------------ motion module (motion_module.py:108-133,173-186)
     def _motion_module(self, m, x, hw_geo, C, out, out_map):
@@ -324,7 +338,7 @@ class ForwardPlan:
         att = self.buf(n + ".att", M, C)
         ff = self.buf(n + ".ff", M, 4 * C)
         stats = torch.empty((self.BT * 32 * 2 * 34,), dtype=torch.float64, device=self.device)
-        self.bufs[n + ".stats"] = stats
+        self.bufs[self._prefix + n + ".stats"] = stats
         self.op(lib.vda_groupnorm_tokens, x.data_ptr(), self.dcode, g.data_ptr(), self.dcode, W_[n + ".gn.w"].data_ptr(),
                 W_[n + ".gn.b"].data_ptr(), 1e-6, self.BT, hw, C, 32, stats.data_ptr(), launches=3)
         self.gemm(g, W_[n + ".in.w"], M, C, C, bias=W_[n + ".in.b"], out=hbuf)
@@ -375,14 +389,17 @@ class ForwardPlan:
                   out_map=out_map)
 
     # ------------------------------------------------------------------ DPTHeadTemporal.forward (dpt_temporal.py:53-99)
-    def _build_head(self, taps, skip_tmp_block):
-        pw, W_, lib = self.pw, self.pw.w, self._lib
-        BT, ph, pwid, D, F, oc = self.BT, self.ph, self.pw_, pw.D, pw.features, pw.oc
+    # The head is built in three stages so that the streaming mode (dpt_temporal.py:132-260) can run them on different
+    # frame counts: reassemble (the new frame), middle (the T-frame temporal context), tail (the frames to predict).
+    def _reassemble(self, taps):
+        """projects (1x1) + resize layers (dpt.py:50-90; dpt_temporal.py:55-69).  Returns layer_1, layer_2 (padded) and
+        layer_3, layer_4 (dense)."""
+        pw, W_ = self.pw, self.pw.w
+        BT, ph, pwid, D, oc = self.BT, self.ph, self.pw_, pw.D, pw.oc
         P = ph * pwid
         geo3 = (BT, ph, pwid)
         h1, w1, h2, w2, h3, w3 = 4 * ph, 4 * pwid, 2 * ph, 2 * pwid, ph, pwid
         h4, w4 = (ph + 1) // 2, (pwid + 1) // 2
-        # reassemble: projects (1x1) + resize layers (dpt.py:50-90)
         t0 = self.buf("t0", BT * P, oc[0])
         self.gemm(taps[0], W_["proj0.w"], BT * P, oc[0], D, bias=W_["proj0.b"], out=t0)
         l1 = self.padded("layer_1", h1, w1, oc[0])
@@ -399,44 +416,64 @@ class ForwardPlan:
         self.gemm(taps[3], W_["proj3.w"], BT * P, oc[3], D, geo=geo3, bias=W_["proj3.b"], out=t3, out_map=L.MAP_PADDED)
         l4 = self.buf("layer_4", BT * h4 * w4, oc[3])
         self.conv3x3(t3, "rs3.w", h3, w3, oc[3], oc[3], bias=W_["rs3.b"], out=l4, out_map=L.MAP_STRIDE2)
-        # motion modules 0/1 on layer_3 / layer_4 (dpt_temporal.py:75-76)
+        return l1, l2, l3, l4
+
+    def _rn(self, i, src, h, w):
+        """scratch.layer{i}_rn (3x3, no bias; blocks.py:20-33): raw + relu copies, both padded."""
+        F, oc = self.pw.features, self.pw.oc
+        raw = self.padded(f"l{i}r", h, w, F)
+        relu = self.padded(f"l{i}r_relu", h, w, F)
+        self.conv3x3(src, f"rn{i}.w", h, w, oc[i - 1], F, out=raw, out_relu=relu)
+        return raw, relu
+
+    def _head_middle(self, l3, l4, skip_tmp_block):
+        """Motion modules 0/1, layer3/4_rn, refinenet4 (+ motion module 2), refinenet3 + motion module 3
+        (dpt_temporal.py:75-76,80-87) over self.BT = batch * T frames.  Returns path_3 (padded at the layer_2 size)."""
+        pw = self.pw
+        ph, pwid, F, oc = self.ph, self.pw_, pw.features, pw.oc
+        BT = self.BT
+        h2, w2, h3, w3 = 2 * ph, 2 * pwid, ph, pwid
+        h4, w4 = (ph + 1) // 2, (pwid + 1) // 2
         l3m = self.padded("mm0", h3, w3, oc[2])
         self._motion_module(0, l3, (h3, w3), oc[2], l3m, L.MAP_PADDED)
         l4m = self.padded("mm1", h4, w4, oc[3])
         self._motion_module(1, l4, (h4, w4), oc[3], l4m, L.MAP_PADDED)
-        # layerN_rn (3x3, no bias), raw + relu copies (dpt_temporal.py:78-81)
-        rn, rn_relu = {}, {}
-        for i, (src, h, w) in enumerate(((l1, h1, w1), (l2, h2, w2), (l3m, h3, w3), (l4m, h4, w4)), start=1):
-            rn[i] = self.padded(f"l{i}r", h, w, F)
-            rn_relu[i] = self.padded(f"l{i}r_relu", h, w, F)
-            self.conv3x3(src, f"rn{i}.w", h, w, oc[i - 1], F, out=rn[i], out_relu=rn_relu[i])
-        # refinenet4 (+ motion module 2) (dpt_temporal.py:83-85)
+        rn3, rn3_relu = self._rn(3, l3m, h3, w3)
+        rn4, rn4_relu = self._rn(4, l4m, h4, w4)
         if skip_tmp_block:
             p4 = self.padded("path_4", h3, w3, F)
-            self._fusion(4, rn[4], rn_relu[4], None, None, h4, w4, h3, w3, p4, L.MAP_PADDED)
+            self._fusion(4, rn4, rn4_relu, None, None, h4, w4, h3, w3, p4, L.MAP_PADDED)
         else:
             p4d = self.buf("path_4d", BT * h3 * w3, F)
-            self._fusion(4, rn[4], rn_relu[4], None, None, h4, w4, h3, w3, p4d, L.MAP_SAME)
+            self._fusion(4, rn4, rn4_relu, None, None, h4, w4, h3, w3, p4d, L.MAP_SAME)
             p4 = self.padded("path_4", h3, w3, F)
             self._motion_module(2, p4d, (h3, w3), F, p4, L.MAP_PADDED)
-        # refinenet3 + motion module 3 (dpt_temporal.py:86-87)
         p3d = self.buf("path_3d", BT * h2 * w2, F)
-        self._fusion(3, p4, None, rn[3], rn_relu[3], h3, w3, h2, w2, p3d, L.MAP_SAME)
+        self._fusion(3, p4, None, rn3, rn3_relu, h3, w3, h2, w2, p3d, L.MAP_SAME)
         p3 = self.padded("path_3", h2, w2, F)
         self._motion_module(3, p3d, (h2, w2), F, p3, L.MAP_PADDED)
-        # refinenet2, refinenet1 (dpt_temporal.py:88-89)
+        return p3
+
+    def _head_tail(self, p3, l1, l2):
+        """layer1/2_rn, refinenet2, refinenet1, output_conv1, upsample, the fp32 island output_conv2
+        (dpt_temporal.py:78-79,88-99) over self.BT frames.  Returns depth [BT, H, W] fp32."""
+        pw, W_, lib = self.pw, self.pw.w, self._lib
+        BT, ph, pwid, F = self.BT, self.ph, self.pw_, pw.features
+        h1, w1, h2, w2 = 4 * ph, 4 * pwid, 2 * ph, 2 * pwid
+        rn1, rn1_relu = self._rn(1, l1, h1, w1)
+        rn2, rn2_relu = self._rn(2, l2, h2, w2)
         p2 = self.padded("path_2", h1, w1, F)
-        self._fusion(2, p3, None, rn[2], rn_relu[2], h2, w2, h1, w1, p2, L.MAP_PADDED)
+        self._fusion(2, p3, None, rn2, rn2_relu, h2, w2, h1, w1, p2, L.MAP_PADDED)
         h0, w0 = 2 * h1, 2 * w1
         p1 = self.padded("path_1", h0, w0, F)
-        self._fusion(1, p2, None, rn[1], rn_relu[1], h1, w1, h0, w0, p1, L.MAP_PADDED)
+        self._fusion(1, p2, None, rn1, rn1_relu, h1, w1, h0, w0, p1, L.MAP_PADDED)
         # output_conv1 -> bilinear to (14ph, 14pw) -> fp32 island output_conv2 (dpt_temporal.py:91-99)
         o1 = self.buf("oc1", BT * h0 * w0, F // 2)
         self.conv3x3(p1, "oc1.w", h0, w0, F, F // 2, bias=W_["oc1.b"], out=o1, out_map=L.MAP_DENSE)
         # upsample_bilinear2d is an fp32 op under CUDA autocast: the upsampled map is fp32 and un-rounded in both builds, and
         # so is everything after it (ori_type is fp32, so `out.to(ori_type)` at dpt_temporal.py:99 is a no-op)
         depth = torch.empty((BT, self.H, self.W), dtype=torch.float32, device=self.device)
-        self.bufs["depth"] = depth
+        self.bufs[self._prefix + "depth"] = depth
         if self.use_tc and self.fused_tail and (F // 2) % 32 == 0:
             # bf16 build: interpolation, TF32 tensor-core conv and the ReLU -> 1x1 -> ReLU tail in one kernel
             half = (F // 2) % 64 == 0 and os.environ.get("VDA_HEAD_TF32", "0") != "1"
@@ -450,7 +487,12 @@ class ForwardPlan:
             # fp32 operands: SIMT fp32 FMA in the fp32 build, tcgen05 kind::tf32 in the bf16 build (cuDNN's default for fp32 convs)
             self.gemm(up, W_["oc2.w32"], Mup, 32, F // 2, taps=9, geo=(BT, self.H, self.W), m_padded=1, bias=W_["oc2.b"],
                       out_map=L.MAP_DENSE, head_w=W_["oc2.hw"], head_out=depth, head_b=pw.head_b)
-        self.depth = depth
+        return depth
+
+    def _build_head(self, taps, skip_tmp_block):
+        l1, l2, l3, l4 = self._reassemble(taps)
+        p3 = self._head_middle(l3, l4, skip_tmp_block)
+        self.depth = self._head_tail(p3, l1, l2)
 
     # ------------------------------------------------------------------ execution
     def run(self, x: torch.Tensor) -> torch.Tensor:
@@ -488,3 +530,124 @@ class ForwardPlan:
                 rc = fn(*args, st)
             if rc != 0:
                 raise L.VdaError(f"{fn.__name__} failed (rc={rc}): {lib.vda_last_error().decode(errors='replace')}")
+
+
+class StreamPlan(ForwardPlan):
+    """Launch lists of the streaming single-image mode (reference `forward_single_image` / `foward_single_image`,
+    video_depth.py:67-91, dpt_temporal.py:132-260) for one network size.
+
+    The reference keeps the reassembled features (layer_1..4) of past frames in four host-managed tensors, re-gathers
+    T-1 of them by fancy indexing every frame and shifts the whole store with a copy once it is full
+    (video_depth.py:244-258,281-296).  Here the store is four device rings of `rows` slots + one incoming slot; the
+    encoder stage writes the new frame's features straight into the incoming slot, the context is gathered by
+    `vda_copy_frames` through a device index array (so every stage is a static launch list, replayable as a CUDA graph),
+    and "shifting" the store is an index-table update on the host.
+
+    Stages:  "encode" (one frame: encoder + projects/resize layers)  ->  "middle" (T context frames: motion modules
+    0-3, layer3/4_rn, refinenet4/3)  ->  "tail{n}" (the n frames to predict: layer1/2_rn, refinenet2/1, output convs)
+    -> "commit" (incoming slot -> its ring slot).
+    """
+
+    IDX_CTX, IDX_PRED, IDX_P3, IDX_COMMIT = range(4)
+
+    def __init__(self, pw: PackedWeights, T: int, H: int, W: int, device, rows: int, npreds=(1,), skip_tmp_block=False,
+                 use_tc=None, attn_tc=None):
+        self.rows = int(rows)
+        self.npreds = tuple(sorted(set(int(n) for n in npreds)))
+        self.stages = {}
+        super().__init__(pw, 1, T, H, W, device, skip_tmp_block, use_tc=use_tc, attn_tc=attn_tc)
+
+    def _all_ops(self):
+        return [op for st in self.stages.values() for op in st["ops"]]
+
+    def _end_stage(self, name):
+        self.stages[name] = {"ops": self.ops, "graph": None, "runs": 0}
+        self.ops = []
+
+    def _build(self, skip_tmp_block):
+        pw, lib = self.pw, self._lib
+        T, ph, pwid, F, oc = self.T, self.ph, self.pw_, pw.features, pw.oc
+        P = ph * pwid
+        h1, w1, h2, w2 = 4 * ph, 4 * pwid, 2 * ph, 2 * pwid
+        h4, w4 = (ph + 1) // 2, (pwid + 1) // 2
+        R = self.rows
+        esz = 2 if self.bf16 else 4
+        # feature store: zero-initialised like the reference's (video_depth.py:228-231); slot R is the incoming frame
+        shapes = [((h1 + 2) * (w1 + 2), oc[0]), ((h2 + 2) * (w2 + 2), oc[1]), (P, oc[2]), (h4 * w4, oc[3])]
+        self.rings = [torch.zeros((R + 1, r, c), dtype=self.adt, device=self.device) for r, c in shapes]
+        self.frame_bytes = [r * c * esz for r, c in shapes]
+        width = max(T, R + 1, max(self.npreds))
+        self.idx = torch.zeros((4, width), dtype=torch.int32, device=self.device)
+
+        # ---- encode: one frame
+        self.BT, self._prefix = 1, "enc."
+        self._alias = {f"layer_{k + 1}": self.rings[k][R] for k in range(4)}
+        self._reassemble(self._build_encoder())
+        assert not self._alias
+        self._end_stage("encode")
+
+        # ---- middle: the T-frame context (T-1 stored frames + the incoming one)
+        self.BT, self._prefix = T, "mid."
+        l3 = self.buf("l3in", T * P, oc[2])
+        l4 = self.buf("l4in", T * h4 * w4, oc[3])
+        ctx = self.idx[self.IDX_CTX].data_ptr()
+        self.op(lib.vda_copy_frames, self.rings[2].data_ptr(), l3.data_ptr(), ctx, None, T, self.frame_bytes[2])
+        self.op(lib.vda_copy_frames, self.rings[3].data_ptr(), l4.data_ptr(), ctx, None, T, self.frame_bytes[3])
+        p3 = self._head_middle(l3, l4, skip_tmp_block)
+        p3_bytes = (h2 + 2) * (w2 + 2) * F * esz
+        self._end_stage("middle")
+
+        # ---- tails: the frames that get a depth map (dpt_temporal.py:187-192,222-227)
+        self.depths = {}
+        for n in self.npreds:
+            self.BT, self._prefix = n, f"tail{n}."
+            l1 = self.padded("l1in", h1, w1, oc[0])
+            l2 = self.padded("l2in", h2, w2, oc[1])
+            p3s = self.padded("p3in", h2, w2, F)
+            pred = self.idx[self.IDX_PRED].data_ptr()
+            self.op(lib.vda_copy_frames, self.rings[0].data_ptr(), l1.data_ptr(), pred, None, n, self.frame_bytes[0])
+            self.op(lib.vda_copy_frames, self.rings[1].data_ptr(), l2.data_ptr(), pred, None, n, self.frame_bytes[1])
+            self.op(lib.vda_copy_frames, p3.data_ptr(), p3s.data_ptr(), self.idx[self.IDX_P3].data_ptr(), None, n, p3_bytes)
+            self.depths[n] = self._head_tail(p3s, l1, l2)
+            self._end_stage(f"tail{n}")
+
+        # ---- commit: incoming slot -> ring slot idx[IDX_COMMIT][0]
+        dst = self.idx[self.IDX_COMMIT].data_ptr()
+        for k in range(4):
+            self.op(lib.vda_copy_frames, self.rings[k][R].data_ptr(), self.rings[k].data_ptr(), None, dst, 1, self.frame_bytes[k])
+        self._end_stage("commit")
+        self.BT, self._prefix = 1, ""
+        self.depth = None
+
+    # ------------------------------------------------------------------ execution
+    def index_row(self, ctx=(), pred=(), p3=(), commit=()):
+        """One step's index arrays as a host int32 [4, width] block (ring slots / context positions)."""
+        row = torch.zeros(tuple(self.idx.shape), dtype=torch.int32)
+        for r, vals in ((self.IDX_CTX, ctx), (self.IDX_PRED, pred), (self.IDX_P3, p3), (self.IDX_COMMIT, commit)):
+            if len(vals):
+                row[r, :len(vals)] = torch.as_tensor(list(vals), dtype=torch.int32)
+        return row
+
+    def load_indices(self, row_dev):
+        """Make a step's index block current (device-to-device, stream ordered: no host buffer is reused in flight)."""
+        self.idx.copy_(row_dev, non_blocking=True)
+
+    def run_stage(self, name):
+        st = self.stages[name]
+        if st["graph"] is not None:
+            st["graph"].replay()
+            return
+        self.ops = st["ops"]
+        self._launch_ops()
+        st["runs"] += 1
+        if self.use_graph and st["runs"] == 2 and not torch.cuda.is_current_stream_capturing():
+            g = torch.cuda.CUDAGraph()
+            try:
+                with torch.cuda.graph(g):
+                    self._launch_ops()
+                st["graph"] = g
+            except Exception:  # capture is an optimisation
+                self.use_graph = False
+
+    def launch(self):
+        raise RuntimeError("StreamPlan runs stage by stage (run_stage)")

@@ -16,7 +16,7 @@ import torch.nn as nn
 
 from . import lib as L
 from .driver import WindowedDepthDriver
-from .engine import ForwardPlan, PackedWeights
+from .engine import ForwardPlan, PackedWeights, StreamPlan
 from .modules import DinoV2Params, DPTHeadTemporalParams
 
 # infer settings, do not change (video_depth.py:29-33); imported by the reference's other files
@@ -70,6 +70,17 @@ class VideoDepthAnything(nn.Module):
             self._plans[key] = p
         return p
 
+    def stream_plan(self, T, H, W, device, bf16, rows, npreds, skip_tmp_block=False):
+        """Plan of the streaming mode for one (context length, network size, store size, prediction counts)."""
+        pw = self._packed_weights(device, bf16)
+        key = (str(device), bf16, "stream", T, H, W, int(rows), tuple(npreds), bool(skip_tmp_block), self.force_simt, self.attn_simt)
+        p = self._plans.get(key)
+        if p is None:
+            p = StreamPlan(pw, T, H, W, device, rows, npreds, skip_tmp_block, use_tc=bf16 and not self.force_simt,
+                           attn_tc=bf16 and not self.force_simt and not self.attn_simt)
+            self._plans[key] = p
+        return p
+
     # ------------------------------------------------------------------ forward (video_depth.py:58-65)
     def forward(self, x, skip_tmp_block=False):
         B, T, Cc, H, W = x.shape
@@ -80,6 +91,21 @@ class VideoDepthAnything(nn.Module):
         # fp32 in both builds: under CUDA autocast the head's bilinear upsample is an fp32 op, so the output convs and
         # the result stay fp32; the identity resize + ReLU of video_depth.py:63-64 are numerical no-ops.
         return depth.clone().unflatten(0, (B, T))
+
+    # ------------------------------------------------------------------ streaming mode (video_depth.py:93-327)
+    def infere_single_image(self, frames, target_fps, input_size=518, device="cuda", fp32=False, warmup=True,
+                            inference_length=32, keyframe_list=[0, 12], align_each_new_frame=True, skip_tmp_block=False):
+        """One new frame per step against a stored temporal context (the fork's streaming mode).  Same arguments, return
+        value and failure modes as the reference: `warmup=False` raises NotImplementedError (video_depth.py:321-322); with
+        `align_each_new_frame` the first frame only serves the alignment and is dropped from the result (:324-325), and
+        keyframe lists whose rows fall outside the first context raise IndexError as the reference does (its default
+        `[0, 12]` among them -- use keyframes >= 2, or align_each_new_frame=False)."""
+        if not warmup:
+            raise NotImplementedError
+        from .stream import StreamingDepthDriver
+        drv = StreamingDepthDriver(self, device=device, fp32=fp32, skip_tmp_block=skip_tmp_block)
+        depth = drv.run(frames, input_size, inference_length, keyframe_list, align_each_new_frame)
+        return depth, target_fps
 
     # ------------------------------------------------------------------ driver (video_depth.py:329-417)
     def infer_video_depth(self, frames, target_fps, input_size=518, device="cuda", fp32=False, skip_tmp_block=False):
