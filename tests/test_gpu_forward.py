@@ -268,3 +268,42 @@ def test_stream_contract():
         m.infere_single_image(frames, 24, input_size=28, device="cuda", fp32=True, warmup=False)
     with pytest.raises(ValueError):   # fewer frames than the context: nothing to stack
         m.infere_single_image(frames[:20], 24, input_size=28, device="cuda", fp32=True, align_each_new_frame=False)
+
+
+@pytest.mark.parametrize("enc,T,ph,pw", [("vits", 16, 5, 7), ("vits", 64, 4, 6), ("vitl", 16, 3, 4), ("vitl", 64, 2, 3)])
+def test_isolated_head_frames_16_64(enc, T, ph, pw):
+    """BASELINE.json config 5: `DPTHeadTemporal.forward` alone on random taps, 16 and 64 frames (64 needs
+    num_frames=64 at construction), fp32 build vs the oracle and bf16 build vs the autocast oracle."""
+    from video_depth_anything_b200.video_depth import VideoDepthAnything
+    nf = max(T, 32)
+    m = VideoDepthAnything(**MODEL_CONFIGS[enc], num_frames=nf)
+    sd = make_state_dict(enc, num_frames=nf)
+    m.load_state_dict(sd, strict=True)
+    m = m.to(dev).eval()
+    sd = {k: v.to(dev) for k, v in sd.items()}
+    D = m.pretrained.embed_dim
+    g = torch.Generator().manual_seed(31)
+    taps = [torch.randn(T, ph * pw, D, generator=g).to(dev) for _ in range(4)]
+    d = torch.device("cuda", torch.cuda.current_device())
+    old = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        with torch.no_grad():
+            ref32 = omodel.head_forward(sd, taps, ph, pw, T)[:, 0]
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        ref16 = omodel.head_forward(sd, taps, ph, pw, T)[:, 0]
+    outs = {}
+    for bf16 in (False, True):
+        plan = m.head_plan(1, T, 14 * ph, 14 * pw, d, bf16)
+        for t_dst, t_src in zip(plan.taps, taps):
+            t_dst.copy_(t_src.reshape(t_dst.shape))
+        plan.launch()
+        torch.cuda.synchronize()
+        outs[bf16] = plan.depth.clone()
+    e = rel_err_map(outs[False], ref32).max().item()
+    print(f"[head {enc} T{T}] fp32 max rel-err {e:.3e}")
+    assert e <= 1e-3
+    bf16_gate(f"head bf16 {enc} T{T}", outs[True].float(), ref16.float(), ref32)

@@ -532,6 +532,17 @@ class ForwardPlan:
                 raise L.VdaError(f"{fn.__name__} failed (rc={rc}): {lib.vda_last_error().decode(errors='replace')}")
 
 
+class HeadPlan(ForwardPlan):
+    """`DPTHeadTemporal.forward` alone (dpt_temporal.py:53-99): the four encoder taps [frames*ph*pw, D] are inputs
+    (`self.taps`, written by the caller), the output is `self.depth`.  BASELINE.json config 5 (isolated head / motion
+    module timing at 16 / 32 / 64 frames) runs on this plan."""
+
+    def _build(self, skip_tmp_block):
+        P = self.ph * self.pw_
+        self.taps = [self.buf(f"tap{i}", self.BT * P, self.pw.D) for i in range(4)]
+        self._build_head(self.taps, skip_tmp_block)
+
+
 class StreamPlan(ForwardPlan):
     """Launch lists of the streaming single-image mode (reference `forward_single_image` / `foward_single_image`,
     video_depth.py:67-91, dpt_temporal.py:132-260) for one network size.

@@ -166,4 +166,4 @@ class StreamingDepthDriver:
         res = out[1:n] if align else out[:n]  # aligned mode: frame 0 only serves the alignment (video_depth.py:324-327)
         if return_device:
             return res
-        return res.cpu().numpy()
+        return self.io._download(res)

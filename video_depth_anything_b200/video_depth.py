@@ -16,7 +16,7 @@ import torch.nn as nn
 
 from . import lib as L
 from .driver import WindowedDepthDriver
-from .engine import ForwardPlan, PackedWeights, StreamPlan
+from .engine import ForwardPlan, HeadPlan, PackedWeights, StreamPlan
 from .modules import DinoV2Params, DPTHeadTemporalParams
 
 # infer settings, do not change (video_depth.py:29-33); imported by the reference's other files
@@ -67,6 +67,17 @@ class VideoDepthAnything(nn.Module):
         p = self._plans.get(key)
         if p is None:
             p = ForwardPlan(pw, B, T, H, W, device, skip_tmp_block, use_tc=use_tc, keep=keep, attn_tc=use_tc and not self.attn_simt)
+            self._plans[key] = p
+        return p
+
+    def head_plan(self, B, T, H, W, device, bf16, skip_tmp_block=False, keep=()):
+        """Plan of the head alone (taps in, depth out) for x of [B, T, 3, H, W]."""
+        pw = self._packed_weights(device, bf16)
+        use_tc = bf16 and not self.force_simt
+        key = (str(device), bf16, "head", B, T, H, W, bool(skip_tmp_block), use_tc, tuple(sorted(keep)))
+        p = self._plans.get(key)
+        if p is None:
+            p = HeadPlan(pw, B, T, H, W, device, skip_tmp_block, use_tc=use_tc, keep=keep, attn_tc=use_tc)
             self._plans[key] = p
         return p
 
