@@ -179,21 +179,33 @@ __device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r
 __device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
 }
+__device__ __forceinline__ float exp2f_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void mma16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
   asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-template <int TT>
-__global__ void __launch_bounds__(128) temporal_attn_mma_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ o, int hw,
-                                                                int C, int heads, int d, float scale, int items) {
+// SPLIT warps share one (b, p, h) problem: they stage q / k / v together and each takes MT / SPLIT query tiles.  The
+// problem is a latency chain (ldmatrix -> mma -> shuffles -> exp -> mma) and the d = 128 staging tiles allow only two
+// blocks per SM, so two warps per problem double the chains in flight for the same shared memory.
+template <int TT, int SPLIT>
+__global__ void __launch_bounds__(128 * SPLIT) temporal_attn_mma_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ o,
+                                                                        int hw, int C, int heads, int d, float scale,
+                                                                        int items) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   constexpr int NT = TT / 8;   // score n-tiles (keys)
   constexpr int MT = TT / 16;  // m-tiles (queries)
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int item = blockIdx.x * (blockDim.x >> 5) + warp;  // (b, p, h)
-  if (item >= items) return;
+  static_assert(MT % SPLIT == 0, "query tiles per warp");
+  const int lane = threadIdx.x & 31;
+  const int part = (threadIdx.x >> 5) % SPLIT;   // which share of the query tiles
+  const int warp = (threadIdx.x >> 5) / SPLIT;   // problem slot inside the block
+  const int item = blockIdx.x * (blockDim.x / (32 * SPLIT)) + warp;  // (b, p, h)
+  if (item >= items) return;  // both warps of a problem leave together; the barrier below is per problem
   const int h = item % heads;
   const int bp = item / heads;
   const int b = bp / hw, p = bp % hw;
@@ -203,23 +215,31 @@ __global__ void __launch_bounds__(128) temporal_attn_mma_kernel(const bf16* __re
   uint8_t* Vs = Ks + TT * pitch;
   const long long ld = 3LL * C;
   const int vpr = d >> 3;  // 16-byte vectors per row
-  for (int i = lane; i < TT * vpr; i += 32) {
-    const int t = i / vpr, c = i - t * vpr;
-    const bf16* rp = qkv + (((long long)b * TT + t) * hw + p) * ld + h * d + c * 8;
-    *reinterpret_cast<uint4*>(Qs + t * pitch + c * 16) = *reinterpret_cast<const uint4*>(rp);
-    *reinterpret_cast<uint4*>(Ks + t * pitch + c * 16) = *reinterpret_cast<const uint4*>(rp + C);
-    *reinterpret_cast<uint4*>(Vs + t * pitch + c * 16) = *reinterpret_cast<const uint4*>(rp + 2 * C);
-  }
-  __syncwarp();
   const uint32_t qs = (uint32_t)__cvta_generic_to_shared(Qs), ks = (uint32_t)__cvta_generic_to_shared(Ks),
                  vs = (uint32_t)__cvta_generic_to_shared(Vs);
+  // The kernel is HBM bound (q, k, v in, o out) and a warp's rows are short (2 d bytes): every 16-byte piece goes global ->
+  // shared as its own cp.async, ALL of them in flight before the first wait, so a warp keeps 3 T d 2 bytes outstanding
+  // instead of three loads (few warps are resident: the staging tiles of d = 128 take 104 KB per block).
+  for (int i = part * 32 + lane; i < TT * vpr; i += 32 * SPLIT) {
+    const int t = i / vpr, c = i - t * vpr;
+    const bf16* rp = qkv + (((long long)b * TT + t) * hw + p) * ld + h * d + c * 8;
+    const uint32_t off = t * pitch + c * 16;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(qs + off), "l"(rp) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ks + off), "l"(rp + C) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(vs + off), "l"(rp + 2 * C) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  if constexpr (SPLIT == 1) __syncwarp();
+  else asm volatile("bar.sync %0, %1;" ::"r"(1 + warp), "n"(32 * SPLIT) : "memory");
   const int g = lane >> 2, tq = lane & 3;
   // ldmatrix lane -> row / column-half assignments
   const int a_row = lane & 15, a_col = (lane >> 4) * 16;                       // A: 16 rows x (2 x 8 cols)
   const int b_row = (lane & 7) + ((lane >> 4) << 3), b_col = ((lane >> 3) & 1) * 16;  // B (two n-tiles): [n][k]
   const int v_row = (lane & 7) + (((lane >> 3) & 1) << 3), v_col = (lane >> 4) * 16;   // V^T (two n-tiles): [k][n]
 #pragma unroll
-  for (int mt = 0; mt < MT; ++mt) {
+  for (int mi = 0; mi < MT / SPLIT; ++mi) {
+    const int mt = part * (MT / SPLIT) + mi;
     float sc[NT][4];
 #pragma unroll
     for (int n = 0; n < NT; ++n) sc[n][0] = sc[n][1] = sc[n][2] = sc[n][3] = 0.f;
@@ -250,10 +270,12 @@ __global__ void __launch_bounds__(128) temporal_attn_mma_kernel(const bf16* __re
     float s0 = 0.f, s1 = 0.f;
 #pragma unroll
     for (int n = 0; n < NT; ++n) {
-      sc[n][0] = expf(sc[n][0] - mx0);
-      sc[n][1] = expf(sc[n][1] - mx0);
-      sc[n][2] = expf(sc[n][2] - mx1);
-      sc[n][3] = expf(sc[n][3] - mx1);
+      // ex2.approx on (x - max) log2 e: 2^-22 relative, far inside the bf16 rounding of the probabilities that follows;
+      // libm expf and the fp32 divisions below were most of this kernel's instructions at head dim 32 (SM bound, not HBM)
+      sc[n][0] = exp2f_approx((sc[n][0] - mx0) * 1.4426950408889634f);
+      sc[n][1] = exp2f_approx((sc[n][1] - mx0) * 1.4426950408889634f);
+      sc[n][2] = exp2f_approx((sc[n][2] - mx1) * 1.4426950408889634f);
+      sc[n][3] = exp2f_approx((sc[n][3] - mx1) * 1.4426950408889634f);
       s0 += sc[n][0] + sc[n][1];
       s1 += sc[n][2] + sc[n][3];
     }
@@ -261,13 +283,14 @@ __global__ void __launch_bounds__(128) temporal_attn_mma_kernel(const bf16* __re
     s0 += __shfl_xor_sync(0xffffffffu, s0, 2);
     s1 += __shfl_xor_sync(0xffffffffu, s1, 1);
     s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
+    const float r0 = __frcp_rn(s0), r1 = __frcp_rn(s1);
     uint32_t pa[NT / 2][4];  // P as A fragments: k-step n2 covers keys 16 n2 .. 16 n2 + 15
 #pragma unroll
     for (int n2 = 0; n2 < NT / 2; ++n2) {
-      pa[n2][0] = pack_bf16x2(sc[2 * n2][0] / s0, sc[2 * n2][1] / s0);
-      pa[n2][1] = pack_bf16x2(sc[2 * n2][2] / s1, sc[2 * n2][3] / s1);
-      pa[n2][2] = pack_bf16x2(sc[2 * n2 + 1][0] / s0, sc[2 * n2 + 1][1] / s0);
-      pa[n2][3] = pack_bf16x2(sc[2 * n2 + 1][2] / s1, sc[2 * n2 + 1][3] / s1);
+      pa[n2][0] = pack_bf16x2(sc[2 * n2][0] * r0, sc[2 * n2][1] * r0);
+      pa[n2][1] = pack_bf16x2(sc[2 * n2][2] * r1, sc[2 * n2][3] * r1);
+      pa[n2][2] = pack_bf16x2(sc[2 * n2 + 1][0] * r0, sc[2 * n2 + 1][1] * r0);
+      pa[n2][3] = pack_bf16x2(sc[2 * n2 + 1][2] * r1, sc[2 * n2 + 1][3] * r1);
     }
     // O = P V, 16 output columns at a time; written into the (already consumed) Q rows of this m-tile
     for (int n0 = 0; n0 < d; n0 += 16) {
@@ -287,8 +310,9 @@ __global__ void __launch_bounds__(128) temporal_attn_mma_kernel(const bf16* __re
     }
   }
   __syncwarp();
-  for (int i = lane; i < TT * vpr; i += 32) {
-    const int t = i / vpr, c = i - t * vpr;
+  // each warp stores the rows of its own query tiles
+  for (int i = lane; i < (TT / SPLIT) * vpr; i += 32) {
+    const int t = part * (TT / SPLIT) + i / vpr, c = i % vpr;
     *reinterpret_cast<uint4*>(o + (((long long)b * TT + t) * hw + p) * C + h * d + c * 8) =
         *reinterpret_cast<const uint4*>(Qs + t * pitch + c * 16);
   }
@@ -300,7 +324,8 @@ int launch_temporal_mma(const void* qkv, void* o, int batch, int hw, int C, int 
   const int pitch = 2 * d + 16;
   const int wpb = 4;
   const size_t smem = (size_t)wpb * 3 * TT * pitch;
-  auto kern = temporal_attn_mma_kernel<TT>;
+  constexpr int SPLIT = TT >= 32 ? 2 : 1;
+  auto kern = temporal_attn_mma_kernel<TT, SPLIT>;
   if (smem > 48 * 1024) {
     cudaError_t ce = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (ce != cudaSuccess) {
@@ -309,7 +334,7 @@ int launch_temporal_mma(const void* qkv, void* o, int batch, int hw, int C, int 
     }
   }
   const int items = batch * hw * heads;
-  kern<<<(items + wpb - 1) / wpb, wpb * 32, smem, st>>>((const bf16*)qkv, (bf16*)o, hw, C, heads, d, 1.0f / sqrtf((float)d), items);
+  kern<<<(items + wpb - 1) / wpb, wpb * 32 * SPLIT, smem, st>>>((const bf16*)qkv, (bf16*)o, hw, C, heads, d, 1.0f / sqrtf((float)d), items);
   VDA_CUDA_LAUNCH_CHECK("temporal_attn_mma_kernel");
   return 0;
 }
