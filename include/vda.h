@@ -74,7 +74,7 @@ typedef struct vda_gemm_desc {
   int32_t gb, gh, gw; /* frames, dense grid height / width (0,0,0 when no map needs them)             */
   int32_t m_padded;  /* 1: m runs over the padded (gh+2)x(gw+2) grid                                 */
   /* ---- epilogue: v = acc + bias[n]; v = R(v); v = act(v) ... (R = round-to-bf16 when round_bf16) ---- */
-  const float* bias; /* [N] (conv-transpose: [ct_cout], indexed n % ct_cout) or NULL                  */
+  const float* bias; /* [N] (conv-transpose: [ct_cout], indexed by co) or NULL                        */
   int32_t act;       /* vda_act; GEGLU: B rows are packed in groups of 64 = 32 value rows + 32 gate rows,
                         output column count is N/2                                                   */
   int32_t round_bf16; /* 1: reproduce the autocast rounding points; 0: pure fp32 arithmetic            */
@@ -83,8 +83,10 @@ typedef struct vda_gemm_desc {
   void* out_relu;    /* optional second copy, relu(v)                                                */
   int64_t ldo;
   int32_t out_map;   /* vda_rowmap                                                                   */
-  int32_t ct_k;      /* VDA_MAP_CONVT: kernel = stride; N = ct_k*ct_k*ct_cout, n = (ky*ct_k+kx)*ct_cout+co */
-  int32_t ct_cout;
+  int32_t ct_k;      /* VDA_MAP_CONVT: kernel = stride; N = ct_k*ct_k*ct_stride, n = (ky*ct_k+kx)*ct_stride+co */
+  int32_t ct_cout;   /* real output channels: columns with co >= ct_cout are padding (zero weights) and are not stored */
+  int32_t ct_stride; /* columns per (ky,kx) block, >= ct_cout; 0 means ct_cout.  Padding the block to a multiple of 64
+                        columns keeps narrow transposed convs (48 / 96 channels) on the coalesced epilogue */
   const void* res;   /* optional: v = R(v + res[row, n])                                             */
   const void* res2;  /* optional: v = R(v + res2[row, n])                                            */
   int64_t ldres;

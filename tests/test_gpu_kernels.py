@@ -114,7 +114,7 @@ def test_conv3x3_simt_f32_all_maps():
 
 
 def test_convt_geglu_resid_simt_f32():
-    from video_depth_anything_b200.engine import _convt_pack, _geglu_interleave
+    from video_depth_anything_b200.engine import _convt_pack, _convt_stride, _geglu_interleave
     L, lib = _lib()
     torch.manual_seed(2)
     Bf, Ci, Co, H, W, k = 2, 48, 48, 5, 6, 4
@@ -122,8 +122,14 @@ def test_convt_geglu_resid_simt_f32():
     xd = x.permute(0, 2, 3, 1).reshape(Bf * H * W, Ci).contiguous()
     out = torch.zeros(Bf * (H * k + 2) * (W * k + 2), Co, device=dev)
     run_gemm(L, lib, A=xd, B=_convt_pack(w), lda=Ci, ldb=Ci, rowsA=xd.shape[0], a_dtype=L.F32, b_dtype=L.F32, M=xd.shape[0],
-             N=k * k * Co, K=Ci, taps=1, ksplit=1, gb=Bf, gh=H, gw=W, bias=b, round_bf16=0, out_dtype=L.F32, out=out, ldo=Co,
-             out_map=L.MAP_CONVT, ct_k=k, ct_cout=Co)
+             N=k * k * _convt_stride(Co), K=Ci, taps=1, ksplit=1, gb=Bf, gh=H, gw=W, bias=b, round_bf16=0, out_dtype=L.F32,
+             out=out, ldo=Co, out_map=L.MAP_CONVT, ct_k=k, ct_cout=Co, ct_stride=_convt_stride(Co))
+    # un-padded column blocks (ct_stride = 0 means ct_cout) stay supported
+    out0 = torch.zeros_like(out)
+    run_gemm(L, lib, A=xd, B=w.permute(2, 3, 1, 0).reshape(k * k * Co, Ci).contiguous(), lda=Ci, ldb=Ci, rowsA=xd.shape[0],
+             a_dtype=L.F32, b_dtype=L.F32, M=xd.shape[0], N=k * k * Co, K=Ci, taps=1, ksplit=1, gb=Bf, gh=H, gw=W, bias=b,
+             round_bf16=0, out_dtype=L.F32, out=out0, ldo=Co, out_map=L.MAP_CONVT, ct_k=k, ct_cout=Co)
+    assert torch.equal(out0, out)
     ref = F.conv_transpose2d(x, w, b, stride=k)
     assert stats("convt", _unpad(out, Bf, H * k, W * k), ref)["max_rel_to_peak"] < 1e-5
     # GEGLU (motion_module/attention.py:382-384)

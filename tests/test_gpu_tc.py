@@ -26,7 +26,7 @@ def test_gemm_tc_bias(M, N, K):
 
 
 def test_gemm_tc_epilogues():
-    from video_depth_anything_b200.engine import _convt_pack, _geglu_interleave
+    from video_depth_anything_b200.engine import _convt_pack, _convt_stride, _geglu_interleave
     L, lib = _lib()
     torch.manual_seed(11)
     M, K, N = 1500, 256, 512
@@ -61,22 +61,26 @@ def test_gemm_tc_epilogues():
     run_gemm(L, lib, B=_geglu_interleave(Wg), N=2 * N, bias=_geglu_interleave(bg), act=L.ACT_GEGLU, out=og, ldo=N, **base)
     v, g = R(A.float() @ Wg.float().T + bg).chunk(2, -1)
     bf16_close("tc_geglu", og.float(), R(v * R(F.gelu(g))))
-    # conv-transpose k=2 scatter into a padded map
-    Bf, H, W_, Ci, Co, k = 3, 9, 11, 96, 96, 2
-    x = torch.randn(Bf, Ci, H, W_, device=dev).bfloat16()
-    w = (torch.randn(Ci, Co, k, k, device=dev) * 0.1).bfloat16()
-    b = torch.randn(Co, device=dev)
-    xd = x.permute(0, 2, 3, 1).reshape(-1, Ci).contiguous()
-    out = torch.zeros(Bf * (H * k + 2) * (W_ * k + 2), Co, device=dev, dtype=torch.bfloat16)
-    run_gemm(L, lib, A=xd, B=_convt_pack(w), lda=Ci, ldb=Ci, rowsA=xd.shape[0], a_dtype=L.BF16, b_dtype=L.BF16, M=xd.shape[0],
-             N=k * k * Co, K=Ci, taps=1, ksplit=1, gb=Bf, gh=H, gw=W_, bias=b, round_bf16=1, out_dtype=L.BF16, out=out, ldo=Co,
-             out_map=L.MAP_CONVT, ct_k=k, ct_cout=Co, use_tc=1)
-    ref = R(F.conv_transpose2d(x.float(), w.float(), b, stride=k))
-    bf16_close("tc_convt", _unpad(out, Bf, H * k, W_ * k).float(), ref)
+    # conv-transpose k = s scatter into a padded map; channel counts that are not multiples of 64 (vits: 48, 96) travel in
+    # column blocks padded to 64 / 128 (ct_stride) so the coalesced epilogue applies
+    for (Bf, H, W_, Ci, Co, k) in ((3, 9, 11, 96, 96, 2), (2, 7, 5, 48, 48, 4), (2, 6, 7, 256, 256, 4)):
+        x = torch.randn(Bf, Ci, H, W_, device=dev).bfloat16()
+        w = (torch.randn(Ci, Co, k, k, device=dev) * 0.1).bfloat16()
+        b = torch.randn(Co, device=dev)
+        xd = x.permute(0, 2, 3, 1).reshape(-1, Ci).contiguous()
+        out = torch.zeros(Bf * (H * k + 2) * (W_ * k + 2), Co, device=dev, dtype=torch.bfloat16)
+        run_gemm(L, lib, A=xd, B=_convt_pack(w), lda=Ci, ldb=Ci, rowsA=xd.shape[0], a_dtype=L.BF16, b_dtype=L.BF16, M=xd.shape[0],
+                 N=k * k * _convt_stride(Co), K=Ci, taps=1, ksplit=1, gb=Bf, gh=H, gw=W_, bias=b, round_bf16=1, out_dtype=L.BF16,
+                 out=out, ldo=Co, out_map=L.MAP_CONVT, ct_k=k, ct_cout=Co, ct_stride=_convt_stride(Co), use_tc=1)
+        ref = R(F.conv_transpose2d(x.float(), w.float(), b, stride=k))
+        bf16_close(f"tc_convt_{Co}_{k}", _unpad(out, Bf, H * k, W_ * k).float(), ref)
+        g = out.reshape(Bf, H * k + 2, W_ * k + 2, Co)
+        assert float(g[:, 0].abs().max()) == 0 and float(g[:, :, -1].abs().max()) == 0  # borders untouched
 
 
 @pytest.mark.parametrize("Ci,Co,H,W", [(64, 64, 12, 10), (48, 64, 20, 17), (256, 128, 30, 30), (1024, 256, 19, 19),
-                                        (256, 128, 61, 57), (128, 96, 70, 45)])
+                                        (256, 128, 61, 57), (128, 96, 70, 45), (64, 64, 40, 44), (64, 32, 50, 37),
+                                        (192, 64, 37, 37)])
 def test_conv3x3_tc(Ci, Co, H, W):
     from video_depth_anything_b200.engine import _conv3x3_pack
     L, lib = _lib()

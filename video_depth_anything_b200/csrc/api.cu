@@ -82,8 +82,10 @@ extern "C" int vda_gemm(const vda_gemm_desc* d, vda_stream_t stream) {
   VDA_CHECK_ARG(d->out || d->resid || d->head_out, "vda_gemm: no output");
   const bool needs_geo = d->out_map != VDA_MAP_SAME || d->res_map != VDA_MAP_SAME || d->resid_map != VDA_MAP_SAME;
   VDA_CHECK_ARG(!needs_geo || (d->gh > 0 && d->gw > 0), "vda_gemm: row maps need gh, gw");
-  VDA_CHECK_ARG(d->out_map != VDA_MAP_CONVT || (d->ct_k > 0 && d->ct_cout > 0 && d->N == d->ct_k * d->ct_k * d->ct_cout),
-                "vda_gemm: conv-transpose needs N == ct_k^2 * ct_cout");
+  const int ct_stride = d->ct_stride ? d->ct_stride : d->ct_cout;
+  VDA_CHECK_ARG(d->out_map != VDA_MAP_CONVT || (d->ct_k > 0 && d->ct_cout > 0 && ct_stride >= d->ct_cout && d->ct_cout % 8 == 0 &&
+                                                 d->N == d->ct_k * d->ct_k * ct_stride),
+                "vda_gemm: conv-transpose needs N == ct_k^2 * ct_stride, ct_stride >= ct_cout, ct_cout %% 8 == 0");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   return d->use_tc ? vda_gemm_tc(d, st) : vda_gemm_simt(d, st);
 }

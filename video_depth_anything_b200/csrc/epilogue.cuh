@@ -18,7 +18,7 @@ struct Epi {
   long long ldo, ldres, ldresid;
   int M, N;  // accumulator rows / columns
   int gb, gh, gw, m_padded;
-  int act, out_map, res_map, resid_map, resid_assign, pos_rows, ct_k, ct_cout;
+  int act, out_map, res_map, resid_map, resid_assign, pos_rows, ct_k, ct_cout, ct_stride;
   float head_b;
 };
 
@@ -31,9 +31,16 @@ static inline Epi make_epi(const vda_gemm_desc* d) {
   e.M = d->M; e.N = d->N;
   e.gb = d->gb; e.gh = d->gh; e.gw = d->gw; e.m_padded = d->m_padded;
   e.act = d->act; e.out_map = d->out_map; e.res_map = d->res_map; e.resid_map = d->resid_map;
-  e.resid_assign = d->resid_assign; e.pos_rows = d->pos_rows; e.ct_k = d->ct_k; e.ct_cout = d->ct_cout;
+  e.resid_assign = d->resid_assign; e.pos_rows = d->pos_rows; e.ct_k = d->ct_k; e.ct_cout = d->ct_cout; e.ct_stride = d->ct_stride ? d->ct_stride : d->ct_cout;
   e.head_b = d->head_b;
   return e;
+}
+
+// bias of accumulator column n (conv-transpose: per output channel; padding columns have none)
+__device__ __forceinline__ float epi_bias(const Epi& e, int n) {
+  if (!e.ct_k) return e.bias[n];
+  const int co = n % e.ct_stride;
+  return co < e.ct_cout ? e.bias[co] : 0.f;
 }
 
 struct RowCtx {
@@ -106,7 +113,7 @@ __device__ __forceinline__ void epi_chunk(const Epi& e, const RowCtx& r, int n0,
     for (int i = 0; i < 32; ++i) {
       int n = n0 + i;
       float bvv = 0.f;
-      if (e.bias && n < e.N) bvv = e.bias[e.ct_k ? (n % e.ct_cout) : n];
+      if (e.bias && n < e.N) bvv = epi_bias(e, n);
       float t = acc[i] + bvv;
       if (e.head_w == nullptr) t = R<RB>(t);  // the fused tail is an fp32 island
       if (e.act == VDA_ACT_GELU) t = R<RB>(gelu_erf(t));
@@ -154,21 +161,23 @@ __device__ __forceinline__ void epi_chunk(const Epi& e, const RowCtx& r, int n0,
   int oc0 = c0, owidth = ncols;
   if (e.out_map == VDA_MAP_CONVT) {
     // fast path requires the 32-chunk to sit inside one (ky,kx) block
-    if (e.ct_cout % 32 != 0) {
+    if (e.ct_stride % 32 != 0) {
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
         int n = c0 + i;
         if (n >= ncols) continue;
-        int kk = n / e.ct_cout, co = n % e.ct_cout, ky = kk / e.ct_k, kx = kk % e.ct_k;
+        int kk = n / e.ct_stride, co = n % e.ct_stride, ky = kk / e.ct_k, kx = kk % e.ct_k;
+        if (co >= e.ct_cout) continue;
         long long row = ((long long)r.b * (e.gh * e.ct_k + 2) + r.y * e.ct_k + ky + 1) * (e.gw * e.ct_k + 2) +
                         r.x * e.ct_k + kx + 1;
         reinterpret_cast<TO*>(e.out)[row * e.ldo + co] = from_f32<TO>(v[i]);
       }
       return;
     }
-    int kk = c0 / e.ct_cout, ky = kk / e.ct_k, kx = kk % e.ct_k;
-    oc0 = c0 % e.ct_cout;
+    int kk = c0 / e.ct_stride, ky = kk / e.ct_k, kx = kk % e.ct_k;
+    oc0 = c0 % e.ct_stride;
     owidth = e.ct_cout;
+    if (oc0 >= owidth) return;  // a chunk of padding columns
     orow = ((long long)r.b * (e.gh * e.ct_k + 2) + r.y * e.ct_k + ky + 1) * (e.gw * e.ct_k + 2) + r.x * e.ct_k + kx + 1;
     if (c0 >= ncols) return;
   }

@@ -59,9 +59,12 @@ __device__ __forceinline__ bool epi_fast_ok(const Epi& e, int n) {
   const bool geglu = e.act == VDA_ACT_GEGLU;
   const int ncols = geglu ? (e.N >> 1) : e.N;
   const int c0 = geglu ? (n >> 1) : n;
-  if (e.head_w != nullptr || c0 + 64 > ncols) return false;
+  if (e.head_w != nullptr || c0 >= ncols) return false;
+  // a ragged last chunk (N % 64 != 0, e.g. the 32-channel output_conv1 of vits) stays on this path when it is a plain
+  // store: lanes whose 8 columns lie beyond N are masked (the accumulator columns there are zero: OOB weight rows)
+  if (c0 + 64 > ncols && ((ncols & 7) || geglu || e.res != nullptr || e.res2 != nullptr || e.resid != nullptr)) return false;
   if ((e.ldo & 7) || (e.ldres & 7) || (e.ldresid & 3)) return false;
-  if (e.out_map == VDA_MAP_CONVT && (e.ct_cout & 63)) return false;
+  if (e.out_map == VDA_MAP_CONVT && (e.ct_stride & 63)) return false;
   return true;
 }
 
@@ -92,9 +95,11 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
   const int col = (GEGLU ? ((n0 + c) >> 1) : (n0 + c)) + 8 * j;  // first of this lane's 8 output columns
   int ocol = col;
   int row_add = 0;
+  bool col_ok = GEGLU || col < e.N;  // false: this lane's 8 columns are padding (ragged last chunk / conv-transpose)
   if (e.out_map == VDA_MAP_CONVT) {
-    const int kk = col / e.ct_cout;
-    ocol = col - kk * e.ct_cout;
+    const int kk = col / e.ct_stride;
+    ocol = col - kk * e.ct_stride;
+    col_ok = col_ok && ocol < e.ct_cout;
     row_add = (kk / e.ct_k) * (e.gw * e.ct_k + 2) + (kk % e.ct_k);
   }
   // EK_RES: the skip operand in phase-2 coordinates (8 lanes cover the 128 B of a row segment), requested before the
@@ -236,7 +241,7 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
     const uint4 p = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((j ^ (rr & 7)) << 4));
     const int orow = __shfl_sync(0xffffffffu, ri.out_row, rr);
     const int drow = __shfl_sync(0xffffffffu, ri.resid_row, rr);
-    if (orow < 0) continue;
+    if (orow < 0 || !col_ok) continue;
     if constexpr (RESK) {  // bf16 add of the reference: R(R(acc + bias) + skip)
       const uint32_t* w = reinterpret_cast<const uint32_t*>(&rv[t]);
       const uint32_t* q = reinterpret_cast<const uint32_t*>(&p);

@@ -152,7 +152,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       float* sbias = sbias_all + acc * BN;
       for (int i = et; i < BN; i += NUM_EPI_WARPS * 32) {
         const int n = n0 + i;
-        sbias[i] = (e.bias != nullptr && n < a.N) ? e.bias[e.ct_k ? (n % e.ct_cout) : n] : 0.f;
+        sbias[i] = (e.bias != nullptr && n < a.N) ? epi_bias(e, n) : 0.f;
       }
       asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
       ptx::mbar_wait(&tfull[acc], acc_phase);
@@ -256,6 +256,16 @@ static bool pair_enabled() {
   if (v < 0) v = env_off("VDA_NO_PAIR") ? 0 : 1;
   return v == 1;
 }
+// smallest N handled by the tap-sharing conv kernel (its weight tile is 128 wide: narrower convs compute zero columns,
+// still far cheaper than nine A loads per tile and an epilogue per 128 x N tile); VDA_CONVSHARE_MIN_N overrides
+static int convshare_min_n() {
+  static int v = -1;
+  if (v < 0) {
+    const char* s = getenv("VDA_CONVSHARE_MIN_N");
+    v = s ? atoi(s) : 32;
+  }
+  return v;
+}
 static bool convshare_enabled() {
   static int v = -1;
   if (v < 0) v = env_off("VDA_NO_CONVSHARE") ? 0 : 1;
@@ -278,7 +288,7 @@ int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
     return launch_tc<32, bf16, true, true>(d, st);
   }
   // 3x3 convolutions: tap-sharing kernel (one A load per three taps, two M tiles per weight tile)
-  if (d->taps == 9 && d->ksplit == 1 && d->N > 64 && d->K % 64 == 0 && d->head_w == nullptr &&
+  if (d->taps == 9 && d->ksplit == 1 && d->N >= convshare_min_n() && d->K % 64 == 0 && d->head_w == nullptr &&
       d->M >= 2048 && convshare_enabled())
     return vda_conv3x3_tc_shared(d, st);
   int bn;

@@ -157,7 +157,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       float* sbias = sbias_all + acc * BN;
       for (int i = et; i < BN; i += NUM_EPI_WARPS * 32) {
         const int n = n0 + i;
-        sbias[i] = (e.bias != nullptr && n < a.N) ? e.bias[e.ct_k ? (n % e.ct_cout) : n] : 0.f;
+        sbias[i] = (e.bias != nullptr && n < a.N) ? epi_bias(e, n) : 0.f;
       }
       asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
       ptx::mbar_wait(&tfull[acc], acc_phase);

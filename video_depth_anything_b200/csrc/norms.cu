@@ -31,21 +31,26 @@ template <> struct VecIO<bf16, 4> {
   }
 };
 
-template <typename TI, typename TO, bool RB>
+// LPR lanes per row (32, 16 or 8): narrow rows (D <= 512 / 256) put two / four rows in a warp, so every lane still has
+// several 16-byte loads in flight -- with a whole warp on a 384-wide fp32 row the kernel sat at half the HBM rate.
+template <typename TI, typename TO, bool RB, int LPR>
 __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x, TO* __restrict__ y,
                                                        const float* __restrict__ w, const float* __restrict__ b, float eps,
                                                        long long rows, int D, int group_rows, int skip_first,
                                                        const float* __restrict__ pe, int pe_group, int pe_T) {
   constexpr int V = 16 / (int)sizeof(TI);    // elements per 16-byte input vector
-  constexpr int MAXV = 1024 / (32 * V);      // vectors per lane for D <= 1024
-  const int lane = threadIdx.x & 31;
-  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= rows) return;
+  constexpr int MAXV = 1024 / (32 * V);      // vectors per lane for D <= 1024 * LPR / 32
+  constexpr int RPW = 32 / LPR;              // rows per warp
+  const int lane = threadIdx.x & (LPR - 1);
+  const int sub = (threadIdx.x & 31) / LPR;
+  const long long row = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RPW + sub;
+  const bool live = row < rows;  // dead rows still take part in the shuffles below
   long long orow = row;
-  if (skip_first) {
+  bool emit = live;
+  if (skip_first && live) {
     long long g = row / group_rows;
     int i = (int)(row % group_rows);
-    if (i == 0) return;
+    if (i == 0) emit = false;
     orow = g * (group_rows - 1) + i - 1;
   }
   const int nv = D / V;
@@ -54,19 +59,21 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x
   float s = 0.f;
 #pragma unroll
   for (int j = 0; j < MAXV; ++j) {
-    const int c = lane + 32 * j;
-    if (c < nv) {
+    const int c = lane + LPR * j;
+    if (c < nv && emit) {
       VecIO<TI, V>::load(xr + c * V, v[j]);
 #pragma unroll
       for (int i = 0; i < V; ++i) s += v[j][i];
     }
   }
-  const float mean = warp_sum(s) / (float)D;
+#pragma unroll
+  for (int o = LPR / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s / (float)D;
   float ss = 0.f;
 #pragma unroll
   for (int j = 0; j < MAXV; ++j) {
-    const int c = lane + 32 * j;
-    if (c < nv) {
+    const int c = lane + LPR * j;
+    if (c < nv && emit) {
 #pragma unroll
       for (int i = 0; i < V; ++i) {
         const float d = v[j][i] - mean;
@@ -74,12 +81,15 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x
       }
     }
   }
-  const float rstd = rsqrtf(warp_sum(ss) / (float)D + eps);
+#pragma unroll
+  for (int o = LPR / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  if (!emit) return;
+  const float rstd = rsqrtf(ss / (float)D + eps);
   const float* per = pe ? pe + (long long)((row / pe_group) % pe_T) * D : nullptr;
   TO* yr = y + orow * D;
 #pragma unroll
   for (int j = 0; j < MAXV; ++j) {
-    const int c = lane + 32 * j;
+    const int c = lane + LPR * j;
     if (c < nv) {
       float wv[V], bv[V], pv[V], o[V];
       VecIO<float, V>::load(w + c * V, wv);
@@ -230,14 +240,23 @@ extern "C" int vda_layernorm(const void* x, int32_t x_dtype, void* y, int32_t y_
   VDA_CHECK_ARG(!pe || (pe_group > 0 && pe_T > 0), "vda_layernorm: pe needs pe_group, pe_T");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int wpb = 8;
-  const unsigned grid = (unsigned)((rows + wpb - 1) / wpb);
-#define LN(TI, TO, RB)                                                                                          \
-  layernorm_kernel<TI, TO, RB><<<grid, wpb * 32, 0, st>>>((const TI*)x, (TO*)y, w, b, eps, rows, D, group_rows, \
-                                                          skip_first, pe, pe_group, pe_T)
+  const int lpr = D <= 256 ? 8 : (D <= 512 ? 16 : 32);
+  const long long rpb = (long long)wpb * (32 / lpr);
+  const unsigned grid = (unsigned)((rows + rpb - 1) / rpb);
+#define LN_(TI, TO, RB, LPR)                                                                                          \
+  layernorm_kernel<TI, TO, RB, LPR><<<grid, wpb * 32, 0, st>>>((const TI*)x, (TO*)y, w, b, eps, rows, D, group_rows, \
+                                                               skip_first, pe, pe_group, pe_T)
+#define LN(TI, TO, RB)                     \
+  do {                                     \
+    if (lpr == 8) LN_(TI, TO, RB, 8);      \
+    else if (lpr == 16) LN_(TI, TO, RB, 16); \
+    else LN_(TI, TO, RB, 32);              \
+  } while (0)
   if (x_dtype == VDA_F32 && y_dtype == VDA_BF16) LN(float, bf16, true);
   else if (x_dtype == VDA_BF16 && y_dtype == VDA_BF16) LN(bf16, bf16, true);
   else if (x_dtype == VDA_F32 && y_dtype == VDA_F32) LN(float, float, false);
   else VDA_CHECK_ARG(false, "vda_layernorm: unsupported dtypes %d -> %d", x_dtype, y_dtype);
+#undef LN_
 #undef LN
   VDA_CUDA_LAUNCH_CHECK("layernorm_kernel");
   return 0;

@@ -28,10 +28,19 @@ def _conv3x3_pack(w: torch.Tensor) -> torch.Tensor:
     return w.permute(0, 2, 3, 1).reshape(co, 9 * ci).contiguous()
 
 
+def _convt_stride(cout: int) -> int:
+    """Columns per (ky, kx) block of a packed transposed conv: the channel count rounded up to a multiple of 64, so
+    that every 64-column epilogue chunk lies inside one block and takes the coalesced path (vits: 48 -> 64, 96 -> 128)."""
+    return (cout + 63) // 64 * 64
+
+
 def _convt_pack(w: torch.Tensor) -> torch.Tensor:
-    """ConvTranspose2d weight [Cin, Cout, k, k] -> [(ky*k+kx)*Cout + co, Cin]."""
+    """ConvTranspose2d weight [Cin, Cout, k, k] -> [(ky*k+kx)*stride + co, Cin], zero rows for co >= Cout."""
     ci, co, k, _ = w.shape
-    return w.permute(2, 3, 1, 0).reshape(k * k * co, ci).contiguous()
+    st = _convt_stride(co)
+    out = torch.zeros((k * k, st, ci), dtype=w.dtype, device=w.device)
+    out[:, :co] = w.permute(2, 3, 1, 0).reshape(k * k, co, ci)
+    return out.reshape(k * k * st, ci).contiguous()
 
 
 def _rope_table(C_: int, max_len: int, device) -> torch.Tensor:
@@ -239,6 +248,7 @@ class ForwardPlan:
         d.ldo = ldo if ldo is not None else (out.shape[1] if out is not None else ncols)
         d.out_map = out_map
         d.ct_k, d.ct_cout = ct_k, ct_cout
+        d.ct_stride = _convt_stride(ct_cout) if ct_k else 0
         d.res, d.res2 = L._ptr(res), L._ptr(res2)
         d.ldres = ldres if ldres is not None else (res.shape[1] if res is not None else d.ldo)
         d.res_map = res_map
@@ -403,12 +413,12 @@ class ForwardPlan:
         t0 = self.buf("t0", BT * P, oc[0])
         self.gemm(taps[0], W_["proj0.w"], BT * P, oc[0], D, bias=W_["proj0.b"], out=t0)
         l1 = self.padded("layer_1", h1, w1, oc[0])
-        self.gemm(t0, W_["rs0.w"], BT * P, 16 * oc[0], oc[0], geo=geo3, bias=W_["rs0.b"], out=l1, out_map=L.MAP_CONVT, ct_k=4,
+        self.gemm(t0, W_["rs0.w"], BT * P, 16 * _convt_stride(oc[0]), oc[0], geo=geo3, bias=W_["rs0.b"], out=l1, out_map=L.MAP_CONVT, ct_k=4,
                   ct_cout=oc[0])
         t1 = self.buf("t1", BT * P, oc[1])
         self.gemm(taps[1], W_["proj1.w"], BT * P, oc[1], D, bias=W_["proj1.b"], out=t1)
         l2 = self.padded("layer_2", h2, w2, oc[1])
-        self.gemm(t1, W_["rs1.w"], BT * P, 4 * oc[1], oc[1], geo=geo3, bias=W_["rs1.b"], out=l2, out_map=L.MAP_CONVT, ct_k=2,
+        self.gemm(t1, W_["rs1.w"], BT * P, 4 * _convt_stride(oc[1]), oc[1], geo=geo3, bias=W_["rs1.b"], out=l2, out_map=L.MAP_CONVT, ct_k=2,
                   ct_cout=oc[1])
         l3 = self.buf("layer_3", BT * P, oc[2])
         self.gemm(taps[2], W_["proj2.w"], BT * P, oc[2], D, bias=W_["proj2.b"], out=l3)

@@ -24,7 +24,7 @@ class GemmDesc(C.Structure):
         ("gb", C.c_int32), ("gh", C.c_int32), ("gw", C.c_int32), ("m_padded", C.c_int32),
         ("bias", C.c_void_p), ("act", C.c_int32), ("round_bf16", C.c_int32), ("out_dtype", C.c_int32),
         ("out", C.c_void_p), ("out_relu", C.c_void_p), ("ldo", C.c_int64), ("out_map", C.c_int32),
-        ("ct_k", C.c_int32), ("ct_cout", C.c_int32),
+        ("ct_k", C.c_int32), ("ct_cout", C.c_int32), ("ct_stride", C.c_int32),
         ("res", C.c_void_p), ("res2", C.c_void_p), ("ldres", C.c_int64), ("res_map", C.c_int32),
         ("resid", C.c_void_p), ("gamma", C.c_void_p), ("pos", C.c_void_p), ("ldresid", C.c_int64),
         ("resid_map", C.c_int32), ("resid_assign", C.c_int32), ("pos_rows", C.c_int32),
