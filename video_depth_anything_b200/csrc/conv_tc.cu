@@ -160,9 +160,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
       ptx::mbar_wait(&tfull[acc], acc_phase);
       ptx::tc_fence_after();
-      const int c = half * 64;
+      // N <= 64: one 64-column chunk per M tile -- the two warp sets take one M tile each instead of column halves
+      const bool narrow = a.N <= 64;
+      const int c = narrow ? 0 : half * 64;
 #pragma unroll 1
-      for (int i = 0; i < 2; ++i) {
+      for (int i = narrow ? half : 0; i < (narrow ? half + 1 : 2); ++i) {
         const int m = m0 + i * BM + q * 32 + lane;
         const uint32_t trow = tmem_base + (acc * 2 + i) * BN + ((uint32_t)(q * 32) << 16);
         if (n0 + c >= a.N) break;

@@ -68,7 +68,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], NUM_EPI_WARPS);
+      ptx::mbar_init(&tempty[s], BN <= 64 ? NUM_EPI_WARPS / 2 : NUM_EPI_WARPS);
     }
     ptx::fence_barrier_init();
   }
@@ -144,23 +144,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int cw = geglu ? 128 : 64;           // accumulator columns per chunk (64 output columns)
     uint8_t* stage = epi_smem + ew * 4096;
     float* sbias_all = reinterpret_cast<float*>(epi_smem + NUM_EPI_WARPS * 4096);
-    int acc = 0;
+    // Narrow tiles (BN <= 64) are one 64-column chunk: interleaving chunks over the two warp sets would idle one of them,
+    // and a tile's epilogue is a single latency chain per scheduler (~5000 clk for a K = 64 1x1 convolution whose
+    // mainloop is four MMAs).  The sets take ALTERNATE tiles instead (set == accumulator stage), two epilogues in flight.
+    constexpr bool SPLIT = BN <= 64;
+    constexpr int SET_THREADS = SPLIT ? NUM_EPI_WARPS * 16 : NUM_EPI_WARPS * 32;
+    const int eti = SPLIT ? (et & (SET_THREADS - 1)) : et;
+    int acc = SPLIT ? half : 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      if (SPLIT && (it & 1) != half) continue;
       const int m0 = (tile / a.tiles_n) * BM, n0 = (tile % a.tiles_n) * BN;
       // bias values of this tile's columns -> smem (double-buffered with the accumulator stage: one barrier per tile)
       float* sbias = sbias_all + acc * BN;
-      for (int i = et; i < BN; i += NUM_EPI_WARPS * 32) {
+      for (int i = eti; i < BN; i += SET_THREADS) {
         const int n = n0 + i;
         sbias[i] = (e.bias != nullptr && n < a.N) ? epi_bias(e, n) : 0.f;
       }
-      asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
+      if constexpr (SPLIT) asm volatile("bar.sync %0, %1;" ::"r"(2 + half), "n"(SET_THREADS) : "memory");
+      else asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
       ptx::mbar_wait(&tfull[acc], acc_phase);
       ptx::tc_fence_after();
       const int m = m0 + q * 32 + lane;
       const RowIdx ri = make_row_idx(e, m);
       const uint32_t trow = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
-      for (int c = half * cw; c < BN; c += 2 * cw) {
+      for (int c = SPLIT ? 0 : half * cw; c < BN; c += SPLIT ? cw : 2 * cw) {
         if (n0 + c >= a.N) break;
         if (c + cw <= BN && epi_fast_ok(e, n0 + c)) {
           if constexpr (EK == EK_GENERIC) {
@@ -185,7 +194,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty[acc]);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      if constexpr (SPLIT) acc_phase ^= 1;
+      else if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
   ptx::tc_fence_before();
