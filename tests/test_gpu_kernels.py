@@ -272,7 +272,8 @@ def test_attention_simt(mode):
         ref = ((q * 0.125) @ k.transpose(-1, -2)).softmax(-1) @ v
         assert stats("attn_simt_f32", o.reshape(frames, ntok, heads, 64).permute(0, 2, 1, 3), ref)["max_rel_to_peak"] < 1e-5
     # temporal attention (motion_module/attention.py:182-211)
-    for (T, hw, C_) in ((4, 6, 64), (32, 5, 192), (32, 3, 1024), (16, 4, 256), (3, 7, 384), (32, 9, 256), (64, 3, 256), (64, 2, 1024)):
+    for (T, hw, C_) in ((4, 6, 64), (32, 5, 192), (32, 3, 1024), (16, 4, 256), (3, 7, 384), (32, 9, 256), (64, 3, 256), (64, 2, 1024),
+                       (32, 7, 64), (16, 6, 64), (64, 3, 192), (32, 4, 384)):
         batch = 2 if T == 4 else 1
         qkv = (torch.randn(batch * T * hw, 3 * C_, device=dev)).to(dt)
         o = torch.zeros(batch * T * hw, C_, device=dev, dtype=dt)

@@ -209,7 +209,8 @@ __global__ void __launch_bounds__(128 * SPLIT) temporal_attn_mma_kernel(const bf
   const int h = item % heads;
   const int bp = item / heads;
   const int b = bp / hw, p = bp % hw;
-  const int pitch = 2 * d + 16;  // bytes per staged row: 16 B of padding keeps ldmatrix conflict-free
+  const int dp = (d + 15) & ~15;  // head dim rounded up to the MMA's k = 16: the extra columns are staged as zeros
+  const int pitch = 2 * dp + 16;  // bytes per staged row: 16 B of padding keeps ldmatrix conflict-free
   uint8_t* Qs = smem_raw + (size_t)warp * 3 * TT * pitch;
   uint8_t* Ks = Qs + TT * pitch;
   uint8_t* Vs = Ks + TT * pitch;
@@ -228,6 +229,14 @@ __global__ void __launch_bounds__(128 * SPLIT) temporal_attn_mma_kernel(const bf
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ks + off), "l"(rp + C) : "memory");
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(vs + off), "l"(rp + 2 * C) : "memory");
   }
+  if (dp != d) {  // d = 8 or 24 (vits): one zero 16-byte piece per row completes the last k-step / output tile
+    for (int t = part * 32 + lane; t < TT; t += 32 * SPLIT) {
+      const uint32_t off = t * pitch + vpr * 16;
+      *reinterpret_cast<uint4*>(Qs + off) = make_uint4(0, 0, 0, 0);
+      *reinterpret_cast<uint4*>(Ks + off) = make_uint4(0, 0, 0, 0);
+      *reinterpret_cast<uint4*>(Vs + off) = make_uint4(0, 0, 0, 0);
+    }
+  }
   asm volatile("cp.async.commit_group;" ::: "memory");
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   if constexpr (SPLIT == 1) __syncwarp();
@@ -243,7 +252,7 @@ __global__ void __launch_bounds__(128 * SPLIT) temporal_attn_mma_kernel(const bf
     float sc[NT][4];
 #pragma unroll
     for (int n = 0; n < NT; ++n) sc[n][0] = sc[n][1] = sc[n][2] = sc[n][3] = 0.f;
-    for (int k0 = 0; k0 < d; k0 += 16) {
+    for (int k0 = 0; k0 < dp; k0 += 16) {
       uint32_t a[4];
       ldsm_x4(qs + (mt * 16 + a_row) * pitch + k0 * 2 + a_col, a[0], a[1], a[2], a[3]);
 #pragma unroll
@@ -293,7 +302,7 @@ __global__ void __launch_bounds__(128 * SPLIT) temporal_attn_mma_kernel(const bf
       pa[n2][3] = pack_bf16x2(sc[2 * n2 + 1][2] * r1, sc[2 * n2 + 1][3] * r1);
     }
     // O = P V, 16 output columns at a time; written into the (already consumed) Q rows of this m-tile
-    for (int n0 = 0; n0 < d; n0 += 16) {
+    for (int n0 = 0; n0 < dp; n0 += 16) {
       float oc[2][4] = {};
 #pragma unroll
       for (int n2 = 0; n2 < NT / 2; ++n2) {
@@ -321,7 +330,7 @@ __global__ void __launch_bounds__(128 * SPLIT) temporal_attn_mma_kernel(const bf
 template <int TT>
 int launch_temporal_mma(const void* qkv, void* o, int batch, int hw, int C, int heads, cudaStream_t st) {
   const int d = C / heads;
-  const int pitch = 2 * d + 16;
+  const int pitch = 2 * ((d + 15) & ~15) + 16;
   const int wpb = 4;
   const size_t smem = (size_t)wpb * 3 * TT * pitch;
   constexpr int SPLIT = TT >= 32 ? 2 : 1;
@@ -435,7 +444,7 @@ extern "C" int vda_temporal_attention(const void* qkv, void* o, int32_t dtype, i
   const bool bf = dtype == VDA_BF16 && round_bf16, f32 = dtype == VDA_F32 && !round_bf16;
   VDA_CHECK_ARG(bf || f32, "vda_temporal_attention: unsupported dtype/rounding combination");
   const int dd = C / heads;
-  if (bf && dd % 16 == 0 && dd <= 128 && (T == 16 || T == 32 || T == 64)) {
+  if (bf && dd % 8 == 0 && dd <= 128 && (T == 16 || T == 32 || T == 64)) {
     if (T == 16) return launch_temporal_mma<16>(qkv, o, batch, hw, C, heads, st);
     if (T == 32) return launch_temporal_mma<32>(qkv, o, batch, hw, C, heads, st);
     return launch_temporal_mma<64>(qkv, o, batch, hw, C, heads, st);
