@@ -205,6 +205,22 @@ int vda_scale_shift(const float* pred, const float* target, int64_t count, doubl
 /* out = max(in*st[0] + st[1], 0) over count elements (video_depth.py:399-412). */
 int vda_scale_clamp(const float* in, float* out, const float* st, int64_t count, vda_stream_t stream);
 
+/* ---- evaluation aligner + metrics (utils/align.py:151-236, utils/metrics.py:92-192, eval.py:163-181) ---- */
+
+/* Least squares of [pred, 1] c = 1/gt over the pixels with valid != 0 and gt != 0 (the reference inverts the MASKED ground
+ * truth, utils/align.py:142-147,152-155; numpy does this in float64): coef[0] = scale = 1/c0, coef[1] = shift = -c1/c0
+ * ((inf, 0) when c0 == 0), so that (pred - shift)/scale is the aligned inverse depth.  The five sums accumulate in f64 in scratch[0..4]; phase bit 0 zeroes
+ * the scratch first, bit 1 solves after accumulating (several calls may feed one fit).  `valid` is a byte mask. */
+int vda_eval_fit(const float* pred, const float* gt, const uint8_t* valid, int64_t count, double* scratch, double* coef,
+                 int32_t phase, vda_stream_t stream);
+
+/* aligned = clip(1 / (a == 0 ? 1e-4 : a), 0, max_depth) with a = clip((pred - shift)/scale, 0, 1) for every pixel
+ * (utils/align.py:228-236, evaluated in f64 like the reference and stored as f32; `aligned` may be NULL), and over the valid pixels the sums behind the reference's metrics
+ * (utils/metrics.py): sums[0..7] = n, sum|d-g|, sum|d-g|/g, sum(d-g)/g, sum(d-g)^2, and the counts of
+ * max(d/g, g/d) > 1.25, 1.25^2, 1.25^3 (f64, zeroed by the call). */
+int vda_eval_apply(const float* pred, const float* gt, const uint8_t* valid, const double* coef, double max_depth,
+                   float* aligned, int64_t count, double* sums, vda_stream_t stream);
+
 /* out = in*st[0] + st[1] over count elements, not clamped: the per-frame alignment of the streaming mode
  * (`infere_single_image`, video_depth.py:310-315). */
 int vda_scale_apply(const float* in, float* out, const float* st, int64_t count, vda_stream_t stream);

@@ -279,3 +279,40 @@ def infere_single_image(frames, target_fps, step_fn, reassemble_fn, input_size=5
     if align_each_new_frame:
         return np.stack(depth_list[1:n], axis=0), target_fps  # the first frame only serves the alignment
     return np.stack(depth_list[:n], axis=0), target_fps
+
+
+# --------------------------------------------------------------------------- evaluation aligner + metrics
+def align_prediction(prediction, ground_truth, valid_depth, max_depth=80.0):
+    """utils/align.py:202-236 with its helpers :142-160 restated on plain numpy: the prediction is raw inverse depth, the
+    ground truth metric depth; least squares of [p, 1] c = 1/gt (float32 `np.linalg.lstsq`) over valid pixels whose
+    ground truth is not zero (inverting the masked array masks those), scale = 1/c0, shift = -c1/c0."""
+    prediction = np.asarray(prediction)
+    ground_truth = np.asarray(ground_truth)
+    valid_depth = np.asarray(valid_depth).astype(bool)
+    with np.errstate(divide="ignore"):
+        inv = 1 / np.ma.array(ground_truth, mask=~valid_depth)
+    mask = ~np.ma.getmaskarray(inv)
+    X = prediction[mask][:, None]
+    X = np.concatenate([X, np.ones((len(X), 1), dtype=X.dtype)], axis=-1)
+    coeffs = np.linalg.lstsq(X, np.ma.getdata(inv)[mask], rcond=None)[0]
+    if np.abs(coeffs[0]) <= 0.0:
+        scale, shift = float("inf"), 0.0
+    else:
+        scale, shift = 1 / coeffs[0], -coeffs[1] / coeffs[0]
+    a = np.clip((prediction - shift) / scale, 0.0, 1.0)
+    a = np.where(a == 0.0, 1e-4, a)
+    return np.clip(1.0 / a, 0.0, max_depth), scale, shift
+
+
+def eval_metrics(prediction, ground_truth, valid_depth):
+    """The reference's CSV columns (utils/metrics.py:24-31 over :92-192), numpy."""
+    v = np.asarray(valid_depth).astype(bool)
+    d, g = np.asarray(prediction)[v], np.asarray(ground_truth)[v]
+    with np.errstate(divide="ignore"):
+        r = np.maximum(d / g, g / d)
+    out = {f"Delta{k}": 1.0 - float((r > 1.25 ** k).mean()) for k in (1, 2, 3)}
+    out["SignedRelative"] = float(((d - g) / g).mean())
+    out["AbsoluteError"] = float(np.abs(d - g).mean())
+    out["AbsoluteRelative"] = float((np.abs(d - g) / g).mean())
+    out["MeanSquaredError"] = float(((d - g) ** 2).mean())
+    return out

@@ -29,3 +29,18 @@ def synthetic_video(n: int, H: int, W: int, seed: int) -> np.ndarray:
         img = img + rng.normal(0, 0.02, img.shape).astype(np.float32)
         out[i] = np.clip(img * 255.0, 0, 255).astype(np.uint8)
     return out
+
+
+def synthetic_eval_case(seed: int, n: int = 3, h: int = 40, w: int = 56):
+    """Evaluation inputs (eval.py:133-166 shapes): metric ground truth with sensor dropouts (zeros) and an irregular
+    validity mask, and a raw inverse-depth prediction that is an affine function of 1/gt plus noise.
+    Returns (prediction f32, ground_truth f32, valid bool), each [n, h, w]."""
+    import numpy as np
+
+    rng = np.random.default_rng(seed)
+    gt = (1.0 + 59.0 * rng.random((n, h, w))).astype(np.float32)
+    valid = rng.random((n, h, w)) > 0.2
+    gt[rng.random((n, h, w)) < 0.03] = 0.0
+    valid &= gt > 0   # the reference's metrics divide by the ground truth of every valid pixel
+    pred = (3.0 / np.maximum(gt, 0.5) + 0.2 + 0.02 * rng.standard_normal((n, h, w))).astype(np.float32)
+    return pred, gt, valid

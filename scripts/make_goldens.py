@@ -36,7 +36,7 @@ import torch  # noqa: E402
 from oracle import driver as odrv  # noqa: E402
 from oracle import model as omodel  # noqa: E402
 from oracle.weights import MODEL_CONFIGS, make_state_dict, param_spec  # noqa: E402
-from oracle.inputs import synthetic_clip, synthetic_video  # noqa: E402
+from oracle.inputs import synthetic_clip, synthetic_eval_case, synthetic_video  # noqa: E402
 
 from video_depth_anything.video_depth import VideoDepthAnything  # noqa: E402
 
@@ -185,12 +185,44 @@ def stream_cases():
         manifest["stream_default_args_error"] = f"IndexError: {e}"
 
 
+def eval_case(name, seed, max_depth):
+    """Reference `align_prediction` + the CSV metrics (utils/align.py, utils/metrics.py) vs the oracle restatement."""
+    from utils import align as ralign
+    from utils import metrics as rmet
+    pred, gt, valid = synthetic_eval_case(seed)
+    ref_al, ref_s, ref_t = ralign.align_prediction(pred, gt, valid, max_depth=max_depth)
+    ora_al, ora_s, ora_t = odrv.align_prediction(pred, gt, valid, max_depth=max_depth)
+    assert np.array_equal(np.asarray(ref_al), ora_al) and ref_s == ora_s and ref_t == ora_t, (ref_s, ora_s, ref_t, ora_t)
+    ref_m = {"Delta1": 1. - rmet.OutlierRatio(ref_al, gt, 1.25, valid), "Delta2": 1. - rmet.OutlierRatio(ref_al, gt, 1.25 ** 2, valid),
+             "Delta3": 1. - rmet.OutlierRatio(ref_al, gt, 1.25 ** 3, valid),
+             "SignedRelative": rmet.SignedRelativeDifference_Error(ref_al, gt, valid),
+             "AbsoluteError": rmet.AbsoluteDifference_Error(ref_al, gt, valid),
+             "AbsoluteRelative": rmet.AbsoluteRelativeDifference_Error(ref_al, gt, valid),
+             "MeanSquaredError": rmet.MeanSquared_Error(ref_al, gt, valid)}
+    ora_m = odrv.eval_metrics(ora_al, gt, valid)
+    for k, v in ref_m.items():
+        assert abs(float(v) - ora_m[k]) <= 1e-6 * max(1.0, abs(float(v))), (k, v, ora_m[k])
+    print(f"{name}: eval oracle == reference; scale {float(ref_s):.5f} shift {float(ref_t):.5f} "
+          + " ".join(f"{k}={float(v):.4f}" for k, v in ref_m.items()))
+    np.savez_compressed(os.path.join(GOLD, f"eval_{name}.npz"), aligned=np.asarray(ref_al)[:, ::2, ::2].astype(np.float32),
+                        scale_shift=np.array([ref_s, ref_t], dtype=np.float64),
+                        metrics=np.array([float(ref_m[k]) for k in sorted(ref_m)], dtype=np.float64),
+                        meta=np.array([seed, int(max_depth)], dtype=np.int64))
+    manifest["cases"][f"eval_{name}"] = {"seed": seed, "max_depth": max_depth, "scale": float(ref_s), "shift": float(ref_t)}
+
+
+def eval_cases():
+    eval_case("s1_d80", 1, 80.0)
+    eval_case("s2_d40", 2, 40.0)
+
+
 def main_new_only():
     """`make_goldens.py --new`: only the cases added after the first golden set (merged into MANIFEST.json)."""
     with open(os.path.join(GOLD, "MANIFEST.json")) as f:
         old = json.load(f)
     forward_case("vits_T8_42x56_rope", "vits", 8, 42, 56, seed=7, pe="rope")
     stream_cases()
+    eval_cases()
     old["cases"].update(manifest["cases"])
     old["stream_default_args_error"] = manifest["stream_default_args_error"]
     with open(os.path.join(GOLD, "MANIFEST.json"), "w") as f:
@@ -227,6 +259,7 @@ if __name__ == "__main__":
     forward_case("vitl_T3_28x42", "vitl", 3, 28, 42, seed=4)
     forward_case("vits_T8_42x56_rope", "vits", 8, 42, 56, seed=7, pe="rope")
     stream_cases()
+    eval_cases()
     driver_case("vits_n50_48x64", "vits", 50, 48, 64, 56, seed=5)
     driver_case("vits_n23_40x90", "vits", 23, 40, 90, 56, seed=6)  # ratio > 1.78 branch
     with open(os.path.join(GOLD, "MANIFEST.json"), "w") as f:

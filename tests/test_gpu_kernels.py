@@ -365,3 +365,41 @@ def test_rope_qk(mode):
         bf16_close("rope_bf16", buf.float(), ref.float(), ulps=1.0, frac=1e-3)
     else:
         assert stats("rope_f32", buf, ref)["max_rel_to_peak"] < 1e-6
+
+
+@pytest.mark.parametrize("case", ["s1_d80", "s2_d40"])
+def test_eval_aligner_and_metrics(case):
+    """the evaluation aligner + metrics on the device (vda_eval_fit / vda_eval_apply behind
+    `evaluation.align_prediction`) vs the real reference's output (golden) and the oracle."""
+    import os
+    from oracle import driver as odrv
+    from oracle.inputs import synthetic_eval_case
+    from tests.util import GOLD
+    from video_depth_anything_b200 import evaluation as pev
+    g = np.load(os.path.join(GOLD, f"eval_{case}.npz"))
+    seed, max_depth = [int(v) for v in g["meta"]]
+    pred, gt, valid = synthetic_eval_case(seed)
+    al, s, t, m = pev.align_prediction(pred, gt, valid, max_depth=float(max_depth), return_metrics=True)
+    assert isinstance(al, np.ndarray) and al.dtype == np.float32 and al.shape == pred.shape
+    # f64 normal equations vs LAPACK's f64 SVD lstsq
+    assert np.allclose([s, t], g["scale_shift"], rtol=1e-8), (s, t, g["scale_shift"])
+    ref = g["aligned"]
+    e = np.abs(al[:, ::2, ::2] - ref) / np.maximum(np.abs(ref), 1e-3 * np.abs(ref).max())
+    print(f"[eval {case}] scale {s:.6f} shift {t:.6f} aligned max rel-err {e.max():.3e}")
+    assert e.max() <= 1e-6
+    assert np.allclose([m[k] for k in sorted(m)], g["metrics"], rtol=1e-6, atol=1e-9), (m, g["metrics"])
+    # device tensors in -> device tensor out, same numbers
+    dp, dg, dv = (torch.from_numpy(x).to(dev) for x in (pred, gt, valid))
+    al2, s2, t2 = pev.align_prediction(dp, dg, dv, max_depth=float(max_depth))
+    # (the f64 block sums are combined with atomics: the last bits of the coefficients depend on the order)
+    assert al2.is_cuda and np.allclose([s2, t2], [s, t], rtol=1e-12) and (al2.cpu().numpy() != al).mean() < 1e-4
+    # with the oracle's coefficients the aligned map is the oracle's bit for bit (same float32 arithmetic)
+    ev = pev.DeviceEvaluator(dev)
+    _, so, to = odrv.align_prediction(pred, gt, valid, max_depth=float(max_depth))
+    coef = torch.tensor([so, to], dtype=torch.float64, device=dev)
+    al3, sums = ev.apply(dp, dg, dv.view(torch.uint8), coef, float(max_depth))
+    oal = odrv.align_prediction(pred, gt, valid, max_depth=float(max_depth))[0].astype(np.float32)
+    assert np.array_equal(al3.cpu().numpy(), oal)
+    mo = odrv.eval_metrics(odrv.align_prediction(pred, gt, valid, max_depth=float(max_depth))[0], gt, valid)
+    md = ev.metrics_from_sums(sums)
+    assert all(abs(md[k] - mo[k]) <= 1e-9 * max(1.0, abs(mo[k])) for k in mo), (md, mo)

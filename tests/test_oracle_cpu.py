@@ -150,6 +150,20 @@ def test_stream_schedule_and_feature_store():
         assert [phys[s] for s in store.slot] == literal
 
 
+@pytest.mark.parametrize("case", ["s1_d80", "s2_d40"])
+def test_oracle_eval_aligner_matches_reference_golden(case):
+    """utils/align.py:202-236 + utils/metrics.py CSV row: oracle restatement vs the real reference's output."""
+    from oracle.inputs import synthetic_eval_case
+    g = _load(f"eval_{case}.npz")
+    seed, max_depth = [int(v) for v in g["meta"]]
+    pred, gt, valid = synthetic_eval_case(seed)
+    al, s, t = odrv.align_prediction(pred, gt, valid, max_depth=float(max_depth))
+    assert np.array_equal(al[:, ::2, ::2].astype(np.float32), g["aligned"])
+    assert np.allclose([s, t], g["scale_shift"], rtol=1e-6)
+    m = odrv.eval_metrics(al, gt, valid)
+    assert np.allclose([m[k] for k in sorted(m)], g["metrics"], rtol=1e-6)
+
+
 def test_window_index_map_golden_and_product():
     from video_depth_anything_b200 import driver as pdrv
 

@@ -123,6 +123,88 @@ __global__ void __launch_bounds__(256) scale_clamp_kernel(const float* __restric
     out[i] = fmaxf(__fadd_rn(__fmul_rn(in[i], s), t), 0.f);
 }
 
+// ---------------------------------------------------------------- evaluation aligner + metrics
+// utils/align.py:151-160,202-226: least squares of [p, 1] c = 1/gt over the pixels that are valid and have gt != 0
+// (the reference inverts the masked ground truth, which masks its zeros), scale = 1/c0, shift = -c1/c0.
+template <int NS, typename F>
+__device__ __forceinline__ void block_sums_to(double* s, double* out, F) {
+  __shared__ double sh[NS][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < NS; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
+    if (lane == 0) sh[k][warp] = s[k];
+  }
+  __syncthreads();
+  if (threadIdx.x < NS) {
+    double t = 0;
+    for (int w = 0; w < 8; ++w) t += sh[threadIdx.x][w];
+    atomicAdd(&out[threadIdx.x], t);
+  }
+}
+
+__global__ void __launch_bounds__(256) eval_fit_sums_kernel(const float* __restrict__ pred, const float* __restrict__ gt,
+                                                           const uint8_t* __restrict__ valid, long long count,
+                                                           double* __restrict__ sums) {
+  double s[5] = {0, 0, 0, 0, 0};  // sum p*p, sum p, sum p*g, sum g, n
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+    const float g0 = gt[i];
+    if (valid[i] && g0 != 0.f) {
+      const double p = pred[i], g = 1.0 / (double)g0;  // `1 / masked float32 array` is a float64 array in numpy
+      s[0] += p * p; s[1] += p; s[2] += p * g; s[3] += g; s[4] += 1.0;
+    }
+  }
+  block_sums_to<5>(s, sums, 0);
+}
+
+__global__ void eval_fit_solve_kernel(const double* __restrict__ sums, double* __restrict__ coef) {
+  const double a00 = sums[0], a01 = sums[1], b0 = sums[2], b1 = sums[3], a11 = sums[4];
+  const double det = a00 * a11 - a01 * a01;
+  double c0 = 0.0, c1 = 0.0;
+  if (det != 0.0) {
+    c0 = (a11 * b0 - a01 * b1) / det;
+    c1 = (-a01 * b0 + a00 * b1) / det;
+  }
+  // float64 throughout, like the reference's lstsq on the float64 target (utils/align.py:155-159)
+  if (fabs(c0) <= 0.0) { coef[0] = (double)INFINITY; coef[1] = 0.0; }   // :156-157
+  else { coef[0] = 1.0 / c0; coef[1] = -c1 / c0; }
+}
+
+// utils/align.py:228-236 + utils/metrics.py:92-192: aligned metric depth of every pixel and the seven error sums over
+// the valid ones.  sums: n, |d-g|, |d-g|/g, (d-g)/g, (d-g)^2, and the outlier counts max(d/g, g/d) > 1.25, 1.25^2, 1.25^3.
+__global__ void __launch_bounds__(256) eval_apply_kernel(const float* __restrict__ pred, const float* __restrict__ gt,
+                                                        const uint8_t* __restrict__ valid, const double* __restrict__ coef,
+                                                        double max_depth, float* __restrict__ aligned, long long count,
+                                                        double* __restrict__ sums) {
+  // the reference's aligned map is a float64 array ((float32 - float64 scalar) / float64 scalar): the arithmetic below
+  // is double, the stored map is its float32 rounding
+  const double scale = coef[0], shift = coef[1];
+  const double t1 = 1.25, t2 = 1.25 * 1.25, t3 = 1.25 * 1.25 * 1.25;
+  double s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+    double a = ((double)pred[i] - shift) / scale;
+    a = fmin(fmax(a, 0.0), 1.0);
+    if (a == 0.0) a = 1e-4;
+    const double d = fmin(fmax(1.0 / a, 0.0), max_depth);
+    if (aligned) aligned[i] = (float)d;
+    if (valid[i]) {
+      const double g = gt[i];
+      const double diff = d - g;
+      const double r = fmax(d / g, g / d);
+      s[0] += 1.0;
+      s[1] += fabs(diff);
+      s[2] += fabs(diff) / g;
+      s[3] += diff / g;
+      s[4] += diff * diff;
+      s[5] += r > t1 ? 1.0 : 0.0;
+      s[6] += r > t2 ? 1.0 : 0.0;
+      s[7] += r > t3 ? 1.0 : 0.0;
+    }
+  }
+  block_sums_to<8>(s, sums, 0);
+}
+
 // streaming mode (video_depth.py:313): cur_prediction * scale + shift, NOT clamped
 __global__ void __launch_bounds__(256) scale_apply_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                          const float* __restrict__ st, long long count) {
@@ -212,6 +294,42 @@ extern "C" int vda_scale_clamp(const float* in, float* out, const float* st, int
   if (blocks < 1) blocks = 1;
   scale_clamp_kernel<<<blocks, 256, 0, s>>>(in, out, st, count);
   VDA_CUDA_LAUNCH_CHECK("scale_clamp_kernel");
+  return 0;
+}
+
+extern "C" int vda_eval_fit(const float* pred, const float* gt, const uint8_t* valid, int64_t count, double* scratch,
+                            double* coef, int32_t phase, vda_stream_t stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (phase & 1) {
+    cudaError_t ce = cudaMemsetAsync(scratch, 0, 5 * sizeof(double), s);
+    if (ce != cudaSuccess) {
+      vda_set_error("vda_eval_fit: memset failed: %s", cudaGetErrorString(ce));
+      return (int)ce;
+    }
+  }
+  int blocks = (int)((count + 256 * 8 - 1) / (256 * 8));
+  if (blocks > 4 * vda_sm_count()) blocks = 4 * vda_sm_count();
+  if (blocks < 1) blocks = 1;
+  if (count > 0) eval_fit_sums_kernel<<<blocks, 256, 0, s>>>(pred, gt, valid, count, scratch);
+  if (phase & 2) eval_fit_solve_kernel<<<1, 1, 0, s>>>(scratch, coef);
+  VDA_CUDA_LAUNCH_CHECK("eval_fit kernels");
+  return 0;
+}
+
+extern "C" int vda_eval_apply(const float* pred, const float* gt, const uint8_t* valid, const double* coef, double max_depth,
+                              float* aligned, int64_t count, double* sums, vda_stream_t stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  cudaError_t ce = cudaMemsetAsync(sums, 0, 8 * sizeof(double), s);
+  if (ce != cudaSuccess) {
+    vda_set_error("vda_eval_apply: memset failed: %s", cudaGetErrorString(ce));
+    return (int)ce;
+  }
+  if (count <= 0) return 0;
+  int blocks = (int)((count + 256 * 8 - 1) / (256 * 8));
+  if (blocks > 4 * vda_sm_count()) blocks = 4 * vda_sm_count();
+  if (blocks < 1) blocks = 1;
+  eval_apply_kernel<<<blocks, 256, 0, s>>>(pred, gt, valid, coef, max_depth, aligned, count, sums);
+  VDA_CUDA_LAUNCH_CHECK("eval_apply_kernel");
   return 0;
 }
 
