@@ -39,8 +39,13 @@ enum vda_rowmap {
   VDA_MAP_PADDED = 2,  /* row = (b*(gh+2) + y+1)*(gw+2) + x+1                                      */
   VDA_MAP_STRIDE2 = 3, /* only even y,x: row = (b*gh2 + y/2)*gw2 + x/2, gh2=(gh+1)/2, gw2=(gw+1)/2 */
   VDA_MAP_TOKENS = 4,  /* row = m + m/(gh*gw) + 1  (one class-token row precedes each frame)       */
-  VDA_MAP_CONVT = 5    /* conv-transpose k=s: row = padded index of (b, y*k+ky, x*k+kx) in a
+  VDA_MAP_CONVT = 5,   /* conv-transpose k=s: row = padded index of (b, y*k+ky, x*k+kx) in a
                           (gh*k) x (gw*k) grid; (ky,kx) come from the column index                 */
+  VDA_MAP_S2D = 6,     /* space-to-depth of the PADDED map for a stride-2 3x3 conv: with (Y, X) = (y+1, x+1),
+                          row = (((Y&1)*2 + (X&1))*gb + b)*hp*wp + (Y>>1)*wp + (X>>1), hp = (gh+1)/2 + 1,
+                          wp = (gw+1)/2 + 1: four parity planes of hp x wp pixels per frame (zero where unwritten) */
+  VDA_MAP_CROP = 7     /* dense grid minus its last row and column: valid iff y < gh-1 and x < gw-1,
+                          row = (b*(gh-1) + y)*(gw-1) + x  (the outputs of a stride-2 conv over parity planes) */
 };
 
 enum vda_act { VDA_ACT_NONE = 0, VDA_ACT_GELU = 1, VDA_ACT_GEGLU = 2, VDA_ACT_RELU = 3 };
@@ -72,7 +77,11 @@ typedef struct vda_gemm_desc {
   int32_t ksplit;    /* 1, or 2 when B carries a (hi, lo) bf16 split of fp32 weights along K         */
   /* ---- geometry of the M space ---- */
   int32_t gb, gh, gw; /* frames, dense grid height / width (0,0,0 when no map needs them)             */
-  int32_t m_padded;  /* 1: m runs over the padded (gh+2)x(gw+2) grid                                 */
+  int32_t m_padded;  /* 1: m runs over the padded (gh+2)x(gw+2) grid.
+                        2 (taps = 9 only): stride-2 3x3 conv (dpt.py:83-88) over the four parity planes written through
+                        VDA_MAP_S2D: m runs over ONE plane grid (gb, gh, gw) = (frames, hp, wp), A holds the planes
+                        back to back, off(t) = ((dy&1)*2 + (dx&1))*gb*gh*gw + (dy>>1)*gw + (dx>>1) with (dy, dx) =
+                        (t/3, t%3): only the kept outputs are computed (a quarter of the padded-grid form)        */
   /* ---- epilogue: v = acc + bias[n]; v = R(v); v = act(v) ... (R = round-to-bf16 when round_bf16) ---- */
   const float* bias; /* [N] (conv-transpose: [ct_cout], indexed by co) or NULL                        */
   int32_t act;       /* vda_act; GEGLU: B rows are packed in groups of 64 = 32 value rows + 32 gate rows,

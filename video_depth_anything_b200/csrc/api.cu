@@ -79,6 +79,7 @@ extern "C" int vda_gemm(const vda_gemm_desc* d, vda_stream_t stream) {
   VDA_CHECK_ARG(d->taps == 1 || d->taps == 9, "vda_gemm: taps must be 1 or 9");
   VDA_CHECK_ARG(d->ksplit == 1 || d->ksplit == 2, "vda_gemm: ksplit must be 1 or 2");
   VDA_CHECK_ARG(d->taps == 1 || (d->m_padded && d->gh > 0 && d->gw > 0), "vda_gemm: 3x3 taps need a padded M space");
+  VDA_CHECK_ARG(d->m_padded != 2 || (d->taps == 9 && d->gb > 0), "vda_gemm: m_padded = 2 is the stride-2 3x3 form (taps = 9, gb set)");
   VDA_CHECK_ARG(d->out || d->resid || d->head_out, "vda_gemm: no output");
   const bool needs_geo = d->out_map != VDA_MAP_SAME || d->res_map != VDA_MAP_SAME || d->resid_map != VDA_MAP_SAME;
   VDA_CHECK_ARG(!needs_geo || (d->gh > 0 && d->gw > 0), "vda_gemm: row maps need gh, gw");

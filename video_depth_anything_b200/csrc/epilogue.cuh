@@ -43,6 +43,14 @@ __device__ __forceinline__ float epi_bias(const Epi& e, int n) {
   return co < e.ct_cout ? e.bias[co] : 0.f;
 }
 
+// Row offset of tap t of a 3x3 convolution in the A operand (include/vda.h: taps, m_padded).
+__host__ __device__ __forceinline__ int vda_tap_off(int taps, int t, int m_padded, int gb, int gh, int gw) {
+  if (taps != 9) return 0;
+  const int dy = t / 3, dx = t - dy * 3;
+  if (m_padded == 2) return ((dy & 1) * 2 + (dx & 1)) * gb * gh * gw + (dy >> 1) * gw + (dx >> 1);
+  return (dy - 1) * (gw + 2) + (dx - 1);
+}
+
 struct RowCtx {
   long long out_row, res_row, resid_row;
   int b, y, x, m;
@@ -60,6 +68,14 @@ __device__ __forceinline__ long long map_row(int kind, const Epi& e, int m, int 
       return ((long long)b * gh2 + (y >> 1)) * gw2 + (x >> 1);
     }
     case VDA_MAP_TOKENS: return (long long)m + m / (e.gh * e.gw) + 1;
+    case VDA_MAP_S2D: {
+      const int Y = y + 1, X = x + 1, hp = ((e.gh + 1) >> 1) + 1, wp = ((e.gw + 1) >> 1) + 1;
+      return ((long long)(((Y & 1) * 2 + (X & 1)) * e.gb + b) * hp + (Y >> 1)) * wp + (X >> 1);
+    }
+    case VDA_MAP_CROP: {
+      if (y >= e.gh - 1 || x >= e.gw - 1) ok = false;
+      return ((long long)b * (e.gh - 1) + y) * (e.gw - 1) + x;
+    }
     default: return m;  // VDA_MAP_CONVT resolved per column
   }
 }
@@ -69,7 +85,7 @@ __device__ __forceinline__ RowCtx make_row_ctx(const Epi& e, int m) {
   r.m = m; r.b = 0; r.y = 0; r.x = 0;
   r.valid = m < e.M;
   if (e.gh > 0) {
-    if (e.m_padded) {
+    if (e.m_padded == 1) {
       int W2 = e.gw + 2, H2 = e.gh + 2;
       int xp = m % W2, t = m / W2;
       int yp = t % H2;

@@ -10,7 +10,8 @@ constexpr int TM = 64, TN = 64, TK = 16;
 template <typename TA, typename TB>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const TA* __restrict__ A, const TB* __restrict__ B,
                                                        float* __restrict__ C, int M, int N, int K, int taps, int ksplit,
-                                                       long long lda, long long ldb, long long rowsA, int W2) {
+                                                       long long lda, long long ldb, long long rowsA, int m_padded,
+                                                       int gb, int gh, int gw) {
   __shared__ float As[TK][TM + 4];
   __shared__ float Bs[TK][TN + 4];
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -20,7 +21,7 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const TA* __restrict__ A
   const int lk = (threadIdx.x & 3) * 4;   // 0,4,8,12 : first k loaded
   for (int s = 0; s < ksplit; ++s) {
     for (int t = 0; t < taps; ++t) {
-      const int off = (taps == 9) ? ((t / 3 - 1) * W2 + (t % 3 - 1)) : 0;
+      const int off = vda_tap_off(taps, t, m_padded, gb, gh, gw);
       const long long arow = (long long)m0 + lr + off;
       const bool arow_ok = (m0 + lr < M) && arow >= 0 && arow < rowsA;
       const long long bcol0 = (long long)(s * taps + t) * K;
@@ -88,7 +89,7 @@ int vda_gemm_simt(const vda_gemm_desc* d, cudaStream_t st) {
   const int W2 = d->gw + 2;
 #define LAUNCH(TA, TB)                                                                                        \
   gemm_simt_kernel<TA, TB><<<grid, 256, 0, st>>>((const TA*)d->A, (const TB*)d->B, C, d->M, d->N, d->K, d->taps, \
-                                                 d->ksplit, d->lda, d->ldb, d->rowsA, W2)
+                                                 d->ksplit, d->lda, d->ldb, d->rowsA, d->m_padded, d->gb, d->gh, d->gw)
   if (d->a_dtype == VDA_F32 && d->b_dtype == VDA_F32) LAUNCH(float, float);
   else if (d->a_dtype == VDA_BF16 && d->b_dtype == VDA_BF16) LAUNCH(bf16, bf16);
   else if (d->a_dtype == VDA_BF16 && d->b_dtype == VDA_F32) LAUNCH(bf16, float);

@@ -31,7 +31,7 @@ struct TcCfg {
 struct TcArgs {
   int M, N, K;         // K per tap
   int taps, ksplit;    // K loop = ksplit * taps * ceil(K/64)
-  int W2;              // gw + 2 (tap row offsets)
+  int m_padded, gb, gh, gw;  // tap row offsets (vda_tap_off)
   int tiles_m, tiles_n;
 };
 
@@ -91,7 +91,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < num_kb; ++kb) {
           const int kin = kb % kb_per_tap, st = kb / kb_per_tap;  // st = s*taps + tap
           const int tap = st % a.taps;
-          const int off = (a.taps == 9) ? ((tap / 3 - 1) * a.W2 + (tap % 3 - 1)) : 0;
+          const int off = vda_tap_off(a.taps, tap, a.m_padded, a.gb, a.gh, a.gw);
           ptx::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
           uint8_t* sb = sa + C::A_BYTES;
@@ -216,7 +216,8 @@ int launch_tc(const vda_gemm_desc* d, cudaStream_t st) {
   rc = vda_make_tmap_2d(&tmB, d->B, (uint64_t)d->ksplit * d->taps * d->K, (uint64_t)d->N, (uint64_t)d->ldb * EB, BKE, BN, EB);
   if (rc) return rc;
   TcArgs a;
-  a.M = d->M; a.N = d->N; a.K = d->K; a.taps = d->taps; a.ksplit = d->ksplit; a.W2 = d->gw + 2;
+  a.M = d->M; a.N = d->N; a.K = d->K; a.taps = d->taps; a.ksplit = d->ksplit;
+  a.m_padded = d->m_padded; a.gb = d->gb; a.gh = d->gh; a.gw = d->gw;
   a.tiles_m = (d->M + BM - 1) / BM;
   a.tiles_n = (d->N + BN - 1) / BN;
   const int tiles = a.tiles_m * a.tiles_n;
@@ -298,7 +299,7 @@ int vda_gemm_tc(const vda_gemm_desc* d, cudaStream_t st) {
     return launch_tc<32, bf16, true, true>(d, st);
   }
   // 3x3 convolutions: tap-sharing kernel (one A load per three taps, two M tiles per weight tile)
-  if (d->taps == 9 && d->ksplit == 1 && d->N >= convshare_min_n() && d->K % 64 == 0 && d->head_w == nullptr &&
+  if (d->taps == 9 && d->m_padded == 1 && d->ksplit == 1 && d->N >= convshare_min_n() && d->K % 64 == 0 && d->head_w == nullptr &&
       d->M >= 2048 && convshare_enabled())
     return vda_conv3x3_tc_shared(d, st);
   int bn;

@@ -35,7 +35,7 @@ template <int EK> struct PairCfg {
 
 struct Tc2Args {
   int M, N, K;
-  int taps, ksplit, W2;
+  int taps, ksplit, m_padded, gb, gh, gw;
   int tiles_m, tiles_n;  // pair tiles (256 x 256)
 };
 
@@ -99,7 +99,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int kb = 0; kb < num_kb; ++kb) {
           const int kin = kb % kb_per_tap, st = kb / kb_per_tap;  // st = s*taps + tap
           const int tap = st % a.taps;
-          const int off = (a.taps == 9) ? ((tap / 3 - 1) * a.W2 + (tap % 3 - 1)) : 0;
+          const int off = vda_tap_off(a.taps, tap, a.m_padded, a.gb, a.gh, a.gw);
           ptx::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
@@ -209,7 +209,8 @@ int launch_tc2(const vda_gemm_desc* d, cudaStream_t st) {
   rc = vda_make_tmap_2d(&tmB, d->B, (uint64_t)d->ksplit * d->taps * d->K, (uint64_t)d->N, (uint64_t)d->ldb * 2, BK, BN / 2, 2);
   if (rc) return rc;
   Tc2Args a;
-  a.M = d->M; a.N = d->N; a.K = d->K; a.taps = d->taps; a.ksplit = d->ksplit; a.W2 = d->gw + 2;
+  a.M = d->M; a.N = d->N; a.K = d->K; a.taps = d->taps; a.ksplit = d->ksplit;
+  a.m_padded = d->m_padded; a.gb = d->gb; a.gh = d->gh; a.gw = d->gw;
   a.tiles_m = (d->M + 2 * BM - 1) / (2 * BM);
   a.tiles_n = (d->N + BN - 1) / BN;
   const int tiles = a.tiles_m * a.tiles_n;

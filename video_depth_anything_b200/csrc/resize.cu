@@ -55,6 +55,35 @@ __global__ void __launch_bounds__(256) im2col_patch_kernel(const float* __restri
   A[idx] = from_f32<T>(v);
 }
 
+// bf16 fast path: one thread per 14-pixel patch row (56 contiguous input bytes as seven float2, 28 output bytes as seven
+// bf16 pairs), 42 such rows per patch plus one thread for the zero tail [588, kpad); consecutive threads write
+// consecutive pieces of the same A row.  The element-per-thread form above moved 2 bytes per store instruction.
+__global__ void __launch_bounds__(256) im2col_patch_rows_kernel(const float* __restrict__ x, bf16* __restrict__ A, int H, int W,
+                                                               int kpad, long long tasks) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= tasks) return;
+  const int r = (int)(idx % 43);   // 0..41: (channel, patch row); 42: the padding tail
+  const long long m = idx / 43;
+  bf16* out = A + m * kpad;
+  if (r == 42) {
+    uint32_t* o = reinterpret_cast<uint32_t*>(out + 588);
+    for (int i = 0; i < (kpad - 588) / 2; ++i) o[i] = 0u;
+    return;
+  }
+  const int pw = W / 14, ph = H / 14;
+  const int px = (int)(m % pw);
+  const int py = (int)((m / pw) % ph);
+  const int f = (int)(m / ((long long)pw * ph));
+  const int c = r / 14, i = r - c * 14;
+  const float2* in = reinterpret_cast<const float2*>(x + (((long long)f * 3 + c) * H + py * 14 + i) * W + px * 14);
+  uint32_t* o = reinterpret_cast<uint32_t*>(out + r * 14);
+  float2 v[7];
+#pragma unroll
+  for (int j = 0; j < 7; ++j) v[j] = in[j];
+#pragma unroll
+  for (int j = 0; j < 7; ++j) o[j] = pack_bf16x2(v[j].x, v[j].y);
+}
+
 __global__ void cls_rows_kernel(float* __restrict__ resid, const float* __restrict__ cls, const float* __restrict__ pos,
                                 int frames, int ntok, int D) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -130,7 +159,10 @@ extern "C" int vda_im2col_patch(const float* x, void* A, int32_t a_dtype, int32_
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const long long total = (long long)frames * (H / 14) * (W / 14) * kpad;
   const unsigned grid = (unsigned)((total + 255) / 256);
-  if (a_dtype == VDA_BF16) im2col_patch_kernel<bf16><<<grid, 256, 0, st>>>(x, (bf16*)A, H, W, kpad, total);
+  if (a_dtype == VDA_BF16 && W % 2 == 0 && kpad % 2 == 0 && kpad >= 588 && ((uintptr_t)x % 8) == 0 && ((uintptr_t)A % 4) == 0) {
+    const long long tasks = (long long)frames * (H / 14) * (W / 14) * 43;
+    im2col_patch_rows_kernel<<<(unsigned)((tasks + 255) / 256), 256, 0, st>>>(x, (bf16*)A, H, W, kpad, tasks);
+  } else if (a_dtype == VDA_BF16) im2col_patch_kernel<bf16><<<grid, 256, 0, st>>>(x, (bf16*)A, H, W, kpad, total);
   else im2col_patch_kernel<float><<<grid, 256, 0, st>>>(x, (float*)A, H, W, kpad, total);
   VDA_CUDA_LAUNCH_CHECK("im2col_patch_kernel");
   return 0;

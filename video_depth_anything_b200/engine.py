@@ -422,10 +422,15 @@ class ForwardPlan:
                   ct_cout=oc[1])
         l3 = self.buf("layer_3", BT * P, oc[2])
         self.gemm(taps[2], W_["proj2.w"], BT * P, oc[2], D, bias=W_["proj2.b"], out=l3)
-        t3 = self.padded("t3", h3, w3, oc[3])
-        self.gemm(taps[3], W_["proj3.w"], BT * P, oc[3], D, geo=geo3, bias=W_["proj3.b"], out=t3, out_map=L.MAP_PADDED)
+        # resize_layers[3] is a stride-2 3x3 conv (dpt.py:83-88): projects[3] scatters its output into the four parity
+        # planes of the padded map (VDA_MAP_S2D), the conv then runs over ONE plane grid with per-tap plane offsets
+        # (m_padded = 2) and computes only the outputs that are kept -- a quarter of the rows of the padded-grid form
+        hp, wp = h4 + 1, w4 + 1
+        t3 = self.buf("t3", 4 * BT * hp * wp, oc[3], zero=True)
+        self.gemm(taps[3], W_["proj3.w"], BT * P, oc[3], D, geo=geo3, bias=W_["proj3.b"], out=t3, out_map=L.MAP_S2D)
         l4 = self.buf("layer_4", BT * h4 * w4, oc[3])
-        self.conv3x3(t3, "rs3.w", h3, w3, oc[3], oc[3], bias=W_["rs3.b"], out=l4, out_map=L.MAP_STRIDE2)
+        self.gemm(t3, W_["rs3.w"], BT * hp * wp, oc[3], oc[3], taps=9, geo=(BT, hp, wp), m_padded=2, bias=W_["rs3.b"], out=l4,
+                  out_map=L.MAP_CROP)
         return l1, l2, l3, l4
 
     def _rn(self, i, src, h, w):

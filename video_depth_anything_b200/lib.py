@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libvda_sm100a.so")
 
 F32, BF16 = 0, 1
-MAP_SAME, MAP_DENSE, MAP_PADDED, MAP_STRIDE2, MAP_TOKENS, MAP_CONVT = range(6)
+MAP_SAME, MAP_DENSE, MAP_PADDED, MAP_STRIDE2, MAP_TOKENS, MAP_CONVT, MAP_S2D, MAP_CROP = range(8)
 ACT_NONE, ACT_GELU, ACT_GEGLU, ACT_RELU = range(4)
 
 
