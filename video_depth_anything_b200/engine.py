@@ -569,16 +569,20 @@ class StreamPlan(ForwardPlan):
     `vda_copy_frames` through a device index array (so every stage is a static launch list, replayable as a CUDA graph),
     and "shifting" the store is an index-table update on the host.
 
-    Stages:  "encode" (one frame: encoder + projects/resize layers)  ->  "middle" (T context frames: motion modules
+    Stages:  "encode" (`enc_batch` frames: encoder + projects/resize layers)  ->  "middle" (T context frames: motion modules
     0-3, layer3/4_rn, refinenet4/3)  ->  "tail{n}" (the n frames to predict: layer1/2_rn, refinenet2/1, output convs)
     -> "commit" (incoming slot -> its ring slot).
     """
 
-    IDX_CTX, IDX_PRED, IDX_P3, IDX_COMMIT = range(4)
+    IDX_CTX, IDX_PRED, IDX_P3, IDX_COMMIT, IDX_SRC = range(5)
 
     def __init__(self, pw: PackedWeights, T: int, H: int, W: int, device, rows: int, npreds=(1,), skip_tmp_block=False,
-                 use_tc=None, attn_tc=None):
+                 use_tc=None, attn_tc=None, enc_batch=1):
         self.rows = int(rows)
+        # The encoder has no temporal coupling, so when the frames are all in memory (they are: the API takes the whole
+        # video) the encode stage runs on `enc_batch` consecutive frames at once into as many incoming slots -- the same
+        # per-frame arithmetic, on GEMMs that fill the machine (one 518x518 frame is 44 tiles for 148 SMs).
+        self.enc_batch = max(1, int(enc_batch))
         self.npreds = tuple(sorted(set(int(n) for n in npreds)))
         self.stages = {}
         super().__init__(pw, 1, T, H, W, device, skip_tmp_block, use_tc=use_tc, attn_tc=attn_tc)
@@ -600,14 +604,15 @@ class StreamPlan(ForwardPlan):
         esz = 2 if self.bf16 else 4
         # feature store: zero-initialised like the reference's (video_depth.py:228-231); slot R is the incoming frame
         shapes = [((h1 + 2) * (w1 + 2), oc[0]), ((h2 + 2) * (w2 + 2), oc[1]), (P, oc[2]), (h4 * w4, oc[3])]
-        self.rings = [torch.zeros((R + 1, r, c), dtype=self.adt, device=self.device) for r, c in shapes]
+        EB = self.enc_batch
+        self.rings = [torch.zeros((R + EB, r, c), dtype=self.adt, device=self.device) for r, c in shapes]
         self.frame_bytes = [r * c * esz for r, c in shapes]
-        width = max(T, R + 1, max(self.npreds))
-        self.idx = torch.zeros((4, width), dtype=torch.int32, device=self.device)
+        width = max(T, R + EB, max(self.npreds))
+        self.idx = torch.zeros((5, width), dtype=torch.int32, device=self.device)
 
-        # ---- encode: one frame
-        self.BT, self._prefix = 1, "enc."
-        self._alias = {f"layer_{k + 1}": self.rings[k][R] for k in range(4)}
+        # ---- encode: enc_batch frames into the incoming slots R .. R + enc_batch - 1
+        self.BT, self._prefix = EB, "enc."
+        self._alias = {f"layer_{k + 1}": self.rings[k][R:R + EB].reshape(EB * shapes[k][0], shapes[k][1]) for k in range(4)}
         self._reassemble(self._build_encoder())
         assert not self._alias
         self._end_stage("encode")
@@ -637,19 +642,20 @@ class StreamPlan(ForwardPlan):
             self.depths[n] = self._head_tail(p3s, l1, l2)
             self._end_stage(f"tail{n}")
 
-        # ---- commit: incoming slot -> ring slot idx[IDX_COMMIT][0]
-        dst = self.idx[self.IDX_COMMIT].data_ptr()
+        # ---- commit: incoming slot idx[IDX_SRC][0] -> ring slot idx[IDX_COMMIT][0]
+        src, dst = self.idx[self.IDX_SRC].data_ptr(), self.idx[self.IDX_COMMIT].data_ptr()
         for k in range(4):
-            self.op(lib.vda_copy_frames, self.rings[k][R].data_ptr(), self.rings[k].data_ptr(), None, dst, 1, self.frame_bytes[k])
+            self.op(lib.vda_copy_frames, self.rings[k].data_ptr(), self.rings[k].data_ptr(), src, dst, 1, self.frame_bytes[k])
         self._end_stage("commit")
         self.BT, self._prefix = 1, ""
         self.depth = None
 
     # ------------------------------------------------------------------ execution
-    def index_row(self, ctx=(), pred=(), p3=(), commit=()):
-        """One step's index arrays as a host int32 [4, width] block (ring slots / context positions)."""
+    def index_row(self, ctx=(), pred=(), p3=(), commit=(), src=()):
+        """One step's index arrays as a host int32 [5, width] block (ring slots / context positions)."""
         row = torch.zeros(tuple(self.idx.shape), dtype=torch.int32)
-        for r, vals in ((self.IDX_CTX, ctx), (self.IDX_PRED, pred), (self.IDX_P3, p3), (self.IDX_COMMIT, commit)):
+        for r, vals in ((self.IDX_CTX, ctx), (self.IDX_PRED, pred), (self.IDX_P3, p3), (self.IDX_COMMIT, commit),
+                        (self.IDX_SRC, src)):
             if len(vals):
                 row[r, :len(vals)] = torch.as_tensor(list(vals), dtype=torch.int32)
         return row

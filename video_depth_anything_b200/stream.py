@@ -64,12 +64,13 @@ class FeatureStore:
 
 
 class StreamingDepthDriver:
-    def __init__(self, model, device="cuda", fp32=False, skip_tmp_block=False):
+    def __init__(self, model, device="cuda", fp32=False, skip_tmp_block=False, enc_batch=8):
         self.model = model
         self.io = WindowedDepthDriver(model, device=device, fp32=fp32, skip_tmp_block=skip_tmp_block)
         self.device = self.io.device
         self.fp32 = fp32
         self.skip_tmp_block = skip_tmp_block
+        self.enc_batch = enc_batch   # frames per encoder launch (1 = strictly frame by frame)
         self.lib = L.load()
 
     def run(self, frames, input_size=518, inference_length=32, keyframe_list=(0, 12), align_each_new_frame=True,
@@ -91,7 +92,8 @@ class StreamingDepthDriver:
                     if v >= T - 1:
                         raise IndexError(f"index {v} is out of bounds for dimension 0 with size {T - 1}")
         with torch.cuda.device(self.device), torch.no_grad():
-            plan = self.model.stream_plan(T, nh, nw, self.device, not self.fp32, rows, npreds, self.skip_tmp_block)
+            plan = self.model.stream_plan(T, nh, nw, self.device, not self.fp32, rows, npreds, self.skip_tmp_block,
+                                          enc_batch=self.enc_batch)
             for ring in plan.rings:
                 ring.zero_()
             return self._run(plan, frames, n, fh, fw, nh, nw, T, max_kf, contexts, align_pos, rows, align_each_new_frame,
@@ -100,13 +102,14 @@ class StreamingDepthDriver:
     def _run(self, plan, frames, n, fh, fw, nh, nw, T, max_kf, contexts, align_pos, rows, align, return_device):
         lib, s = self.lib, L.stream_ptr()
         fe = fh * fw
-        R = rows  # the incoming slot
+        R, EB = rows, plan.enc_batch  # incoming slots R .. R + EB - 1: frame i's features land in slot R + i % EB
         store = FeatureStore(rows)
         # ---- host: every step's index block, uploaded once
         blocks, meta = [], []
         for i in range(n):
+            inc = R + i % EB
             if i < T - 1:
-                blocks.append(plan.index_row(commit=[store.write(i)]))
+                blocks.append(plan.index_row(commit=[store.write(i)], src=[inc]))
                 meta.append(None)
                 continue
             k = min(i - (T - 1), len(contexts) - 1)
@@ -119,8 +122,8 @@ class StreamingDepthDriver:
                     abs_idx = [0 if a == 0 else a + (i - (T + max_kf)) + 1 for a in abs_idx]
             else:
                 pred, abs_idx = [], []
-            blocks.append(plan.index_row(ctx=slots + [R], pred=[slots[p] for p in pred] + [R], p3=list(pred) + [T - 1],
-                                         commit=[store.write(i)]))
+            blocks.append(plan.index_row(ctx=slots + [inc], pred=[slots[p] for p in pred] + [inc], p3=list(pred) + [T - 1],
+                                         commit=[store.write(i)], src=[inc]))
             meta.append((len(pred) + 1, abs_idx))
         table = torch.stack(blocks).to(self.device, non_blocking=True)
 
@@ -137,8 +140,15 @@ class StreamingDepthDriver:
                 self.io._upload_preprocess(frames, uploaded, hi, pre, nh, nw)
                 uploaded = hi
             plan.load_indices(table[i])
-            plan.x_in.copy_(pre[i:i + 1], non_blocking=True)
-            plan.run_stage("encode")
+            if i % EB == 0:  # encoder + reassemble for frames i .. i + EB - 1 (a short last batch re-encodes its tail frame)
+                hi = min(n, i + EB)
+                if hi > uploaded:
+                    self.io._upload_preprocess(frames, uploaded, hi, pre, nh, nw)
+                    uploaded = hi
+                plan.x_in[:hi - i].copy_(pre[i:hi], non_blocking=True)
+                if hi - i < EB:
+                    plan.x_in[hi - i:].copy_(pre[hi - 1:hi].expand(EB - (hi - i), -1, -1, -1), non_blocking=True)
+                plan.run_stage("encode")
             if meta[i] is not None:
                 npred, abs_idx = meta[i]
                 plan.run_stage("middle")

@@ -81,14 +81,15 @@ class VideoDepthAnything(nn.Module):
             self._plans[key] = p
         return p
 
-    def stream_plan(self, T, H, W, device, bf16, rows, npreds, skip_tmp_block=False):
+    def stream_plan(self, T, H, W, device, bf16, rows, npreds, skip_tmp_block=False, enc_batch=1):
         """Plan of the streaming mode for one (context length, network size, store size, prediction counts)."""
         pw = self._packed_weights(device, bf16)
-        key = (str(device), bf16, "stream", T, H, W, int(rows), tuple(npreds), bool(skip_tmp_block), self.force_simt, self.attn_simt)
+        key = (str(device), bf16, "stream", T, H, W, int(rows), tuple(npreds), bool(skip_tmp_block), self.force_simt, self.attn_simt,
+               int(enc_batch))
         p = self._plans.get(key)
         if p is None:
             p = StreamPlan(pw, T, H, W, device, rows, npreds, skip_tmp_block, use_tc=bf16 and not self.force_simt,
-                           attn_tc=bf16 and not self.force_simt and not self.attn_simt)
+                           attn_tc=bf16 and not self.force_simt and not self.attn_simt, enc_batch=enc_batch)
             self._plans[key] = p
         return p
 
