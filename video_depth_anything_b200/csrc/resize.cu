@@ -8,32 +8,68 @@ namespace {
 // value = h0*(w0*a + w1*b) + h1*(w0*c + w1*d), computed in fp32 and rounded once to the storage type.
 template <typename T, typename TO>
 __global__ void __launch_bounds__(256) bilinear_kernel(const T* __restrict__ in, TO* __restrict__ out, int ih, int iw,
-                                                      int ipad, int oh, int ow, int opad, int C, float rh, float rw) {
-  // grid = (x-chunks, oh, frames): the row quantities are block-uniform and no 64-bit division is needed
+                                                      int ipad, int oh, int ow, int opad, int C, float rh, float rw,
+                                                      int rows) {
+  // grid = (x-chunks, oh / rows, frames): the row quantities are block-uniform and no 64-bit division is needed.
+  // A thread walks `rows` consecutive output rows of its column and keeps the two horizontally interpolated input rows
+  // (w0*a + w1*b and w0*c + w1*d, unpacked) in registers: the upper one is re-used while the source row index does not
+  // move and the lower one becomes the upper one when it moves by one, so a 2x upsample loads and interpolates one new
+  // input row per two output rows.  One output row per block re-read its input rows from L2 (the 148 -> 296 upsample,
+  // 1.4 GB out, sat at the L2 bandwidth); four fresh corner loads per output row then sat at the issue rate (158
+  // instructions per eight channels, profiles/ncu_bilinear_r01m.txt).
   const int nv = C >> 3;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= ow * nv) return;
   const int ox = idx / nv, cv = idx - ox * nv;
-  const int oy = blockIdx.y, f = blockIdx.z;
-  const float h1r = rh * oy;
-  const int h1 = (int)h1r;
-  const int h1p = (h1 < ih - 1) ? 1 : 0;
-  const float h1l = h1r - h1, h0l = 1.f - h1l;
+  const int f = blockIdx.z;
   const float w1r = rw * ox;
   const int w1 = (int)w1r;
   const int w1p = (w1 < iw - 1) ? 1 : 0;
   const float w1l = w1r - w1, w0l = 1.f - w1l;
   const int IW = iw + 2 * ipad, IH = ih + 2 * ipad;
-  const T* base = in + (((long long)f * IH + h1 + ipad) * IW + w1 + ipad) * C + cv * 8;
-  float a[8], b[8], c[8], d[8], o[8];
-  Vec8<T>::load(base, a);
-  Vec8<T>::load(base + (long long)w1p * C, b);
-  Vec8<T>::load(base + (long long)h1p * IW * C, c);
-  Vec8<T>::load(base + ((long long)h1p * IW + w1p) * C, d);
-#pragma unroll
-  for (int i = 0; i < 8; ++i) o[i] = h0l * (w0l * a[i] + w1l * b[i]) + h1l * (w0l * c[i] + w1l * d[i]);
   const int OW = ow + 2 * opad, OH = oh + 2 * opad;
-  Vec8<TO>::store(out + (((long long)f * OH + oy + opad) * OW + ox + opad) * C + cv * 8, o);
+  const T* col = in + (((long long)f * IH + ipad) * IW + w1 + ipad) * C + cv * 8;
+  TO* ocol = out + (((long long)f * OH + opad) * OW + ox + opad) * C + cv * 8;
+  const long long irow = (long long)IW * C, orow = (long long)OW * C;
+  const int step = w1p * C;
+  float tp[8], bt[8], a[8], b[8], o[8];
+  int top = -2, bot = -2;  // input rows whose horizontal interpolation sits in tp and bt
+  const int oy0 = blockIdx.y * rows, oy1 = min(oy0 + rows, oh);
+  for (int oy = oy0; oy < oy1; ++oy) {
+    const float h1r = rh * oy;
+    const int h1 = (int)h1r;
+    const int h1b = (h1 < ih - 1) ? h1 + 1 : h1;
+    const float h1l = h1r - h1, h0l = 1.f - h1l;
+    if (h1 != top) {
+      if (h1 == bot) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) tp[i] = bt[i];
+      } else {
+        const T* p = col + h1 * irow;
+        Vec8<T>::load(p, a);
+        Vec8<T>::load(p + step, b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) tp[i] = w0l * a[i] + w1l * b[i];
+      }
+      top = h1;
+    }
+    if (h1b != bot) {
+      if (h1b == top) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) bt[i] = tp[i];
+      } else {
+        const T* p = col + h1b * irow;
+        Vec8<T>::load(p, a);
+        Vec8<T>::load(p + step, b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) bt[i] = w0l * a[i] + w1l * b[i];
+      }
+      bot = h1b;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = h0l * tp[i] + h1l * bt[i];
+    Vec8<TO>::store(ocol + oy * orow, o);
+  }
 }
 
 template <typename T>
@@ -140,9 +176,11 @@ extern "C" int vda_bilinear(const void* in, int32_t in_dtype, void* out, int32_t
   const float rh = oh > 1 ? (float)(ih - 1) / (float)(oh - 1) : 0.f;
   const float rw = ow > 1 ? (float)(iw - 1) / (float)(ow - 1) : 0.f;
   VDA_CHECK_ARG(oh <= 65535 && frames <= 65535, "vda_bilinear: oh / frames exceed the grid limits");
-  const dim3 grid((unsigned)((ow * (C / 8) + 255) / 256), (unsigned)oh, (unsigned)frames);
+  static const int rows_env = [] { const char* e = getenv("VDA_BILINEAR_ROWS"); return e ? atoi(e) : 0; }();
+  const int rows = rows_env > 0 ? rows_env : 16;  // output rows per thread (4: 437 us, 8: 362, 16: 344, 37: 338 on 148 -> 296)
+  const dim3 grid((unsigned)((ow * (C / 8) + 255) / 256), (unsigned)((oh + rows - 1) / rows), (unsigned)frames);
   const int ip = in_padded ? 1 : 0, op = out_padded ? 1 : 0;
-#define BL(TI, TO) bilinear_kernel<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, (TO*)out, ih, iw, ip, oh, ow, op, C, rh, rw)
+#define BL(TI, TO) bilinear_kernel<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, (TO*)out, ih, iw, ip, oh, ow, op, C, rh, rw, rows)
   if (in_dtype == VDA_BF16 && out_dtype == VDA_BF16) BL(bf16, bf16);
   else if (in_dtype == VDA_BF16 && out_dtype == VDA_F32) BL(bf16, float);
   else if (in_dtype == VDA_F32 && out_dtype == VDA_F32) BL(float, float);
