@@ -168,6 +168,12 @@ class PackedWeights:
 class ForwardPlan:
     """Buffers + launch list for `VideoDepthAnything.forward` on x[frames=B*T, 3, H, W] (video_depth.py:58-65)."""
 
+    # fusion blocks: VDA_FUSION_CONV_FIRST=1 runs the 1x1 out_conv before the interpolation (see _fusion).  Off by default:
+    # it saves 0.5 of 56.8 ms per vitl clip but rounds in a different place than the reference, so the bf16 build's noise
+    # is no longer correlated with the reference's (vitl T3 28x42: max deviation from the autocast reference 3.5e-2 ->
+    # 4.6e-2 against a gate of 4.0e-2, same accuracy against fp32).
+    conv_first = os.environ.get("VDA_FUSION_CONV_FIRST", "0") == "1"
+
     def __init__(self, pw: PackedWeights, batch: int, T: int, H: int, W: int, device, skip_tmp_block=False, use_tc=None,
                  keep=(), attn_tc=None, fused_tail=True):
         assert H % 14 == 0 and W % 14 == 0, f"Input image size {H}x{W} is not a multiple of patch size 14"  # patch_embed.py:73-74
@@ -393,6 +399,17 @@ class ForwardPlan:
             s, s_relu = x0, x0_relu
         r = self.padded(n + ".r", h, w, F)
         self._rcu(n + ".rcu2", s, s_relu, h, w, F, r)
+        if self.conv_first:
+            # the 1x1 out_conv and the interpolation are both linear and the bilinear weights sum to one (bias included),
+            # so they commute: the conv runs on the (h, w) map -- a quarter of the rows when upsampling 2x -- and the
+            # interpolation writes the block's output.  The conv's rows on the zero ring hold the bias and are never read
+            # (align_corners interpolation stays inside the map).
+            c = self.buf(n + ".c", self.BT * (h + 2) * (w + 2), F)
+            self.gemm(r, W_[n + ".out.w"], self.BT * (h + 2) * (w + 2), F, F, bias=W_[n + ".out.b"], out=c)
+            assert out_map in (L.MAP_PADDED, L.MAP_SAME)
+            self.op(self._lib.vda_bilinear, c.data_ptr(), self.dcode, out.data_ptr(), self.dcode, self.BT, h, w, 1, oh, ow,
+                    1 if out_map == L.MAP_PADDED else 0, F)
+            return
         u = self.buf(n + ".u", self.BT * oh * ow, F)
         self.op(self._lib.vda_bilinear, r.data_ptr(), self.dcode, u.data_ptr(), self.dcode, self.BT, h, w, 1, oh, ow, 0, F)
         self.gemm(u, W_[n + ".out.w"], self.BT * oh * ow, F, F, geo=(self.BT, oh, ow), bias=W_[n + ".out.b"], out=out,
