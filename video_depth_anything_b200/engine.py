@@ -341,18 +341,23 @@ class ForwardPlan:
     # ------------------------------------------------------------------ motion module (motion_module.py:108-133,173-186)
     def _motion_module(self, m, x, hw_geo, C, out, out_map):
         """x: dense tokens [BT*h*w, C] (also the residual).  out: dense or padded buffer receiving proj_out(h) + x."""
+        att, hbuf = self._mm_front(m, x, hw_geo, C)
+        self._mm_back(m, att, hbuf, x, hw_geo, C, out, out_map)
+
+    def _mm_front(self, m, x, hw_geo, C):
+        """The temporally coupled part of motion module m: GroupNorm, proj_in, the first attention block and the second
+        one up to its attention output (motion_module.py:141-164,187-200).  Returns (att, h): the second block's
+        attention output and the residual stream it will be projected onto; everything after is per frame (_mm_back)."""
         pw, W_, lib = self.pw, self.pw.w, self._lib
         h_, w_ = hw_geo
         hw = h_ * w_
         M = self.BT * hw
-        geo = (self.BT, h_, w_)
         n = f"mm{m}"
         g = self.buf(n + ".g", M, C)
         hbuf = self.buf(n + ".h", M, C)
         nbuf = self.buf(n + ".n", M, C)
         qkv = self.buf(n + ".qkv", M, 3 * C)
         att = self.buf(n + ".att", M, C)
-        ff = self.buf(n + ".ff", M, 4 * C)
         stats = torch.empty((self.BT * 32 * 2 * 34,), dtype=torch.float64, device=self.device)
         self.bufs[self._prefix + n + ".stats"] = stats
         self.op(lib.vda_groupnorm_tokens, x.data_ptr(), self.dcode, g.data_ptr(), self.dcode, W_[n + ".gn.w"].data_ptr(),
@@ -370,11 +375,26 @@ class ForwardPlan:
                         int(self.bf16))
             self.op(lib.vda_temporal_attention, qkv.data_ptr(), att.data_ptr(), self.dcode, self.batch, self.T, hw, C, 8,
                     int(self.bf16))
-            self.gemm(att, W_[f"{n}.a{a}.out.w"], M, C, C, bias=W_[f"{n}.a{a}.out.b"], out=hbuf, res=hbuf)
+            if a == 0:
+                self.gemm(att, W_[f"{n}.a{a}.out.w"], M, C, C, bias=W_[f"{n}.a{a}.out.b"], out=hbuf, res=hbuf)
+        return att, hbuf
+
+    def _mm_back(self, m, att, hbuf, x, hw_geo, C, out, out_map):
+        """The per-frame rest of motion module m over self.BT frames: the second attention block's output projection,
+        the feed-forward, proj_out and the module's residual (motion_module.py:165-172,201-210).  hbuf is updated in place."""
+        W_ = self.pw.w
+        h_, w_ = hw_geo
+        M = self.BT * h_ * w_
+        n = f"mm{m}"
+        nbuf = self.bufs.get(self._prefix + n + ".n")  # the front's LayerNorm buffer when both halves run in one stage
+        if nbuf is None or tuple(nbuf.shape) != (M, C):
+            nbuf = self.buf(n + ".n2", M, C)
+        ff = self.buf(n + ".ff", M, 4 * C)
+        self.gemm(att, W_[f"{n}.a1.out.w"], M, C, C, bias=W_[f"{n}.a1.out.b"], out=hbuf, res=hbuf)
         self.layernorm(hbuf, nbuf, W_[n + ".ffln.w"], W_[n + ".ffln.b"], 1e-5, M, C)
         self.gemm(nbuf, W_[n + ".ff1.w"], M, 8 * C, C, bias=W_[n + ".ff1.b"], act=L.ACT_GEGLU, out=ff)
         self.gemm(ff, W_[n + ".ff2.w"], M, C, 4 * C, bias=W_[n + ".ff2.b"], out=hbuf, res=hbuf)
-        self.gemm(hbuf, W_[n + ".po.w"], M, C, C, geo=geo, bias=W_[n + ".po.b"], out=out, out_map=out_map, res=x,
+        self.gemm(hbuf, W_[n + ".po.w"], M, C, C, geo=(self.BT, h_, w_), bias=W_[n + ".po.b"], out=out, out_map=out_map, res=x,
                   res_map=L.MAP_SAME)
         if n in self.keep:
             self.bufs[n] = out
@@ -458,9 +478,11 @@ class ForwardPlan:
         self.conv3x3(src, f"rn{i}.w", h, w, oc[i - 1], F, out=raw, out_relu=relu)
         return raw, relu
 
-    def _head_middle(self, l3, l4, skip_tmp_block):
+    def _head_middle(self, l3, l4, skip_tmp_block, split_mm3=False):
         """Motion modules 0/1, layer3/4_rn, refinenet4 (+ motion module 2), refinenet3 + motion module 3
-        (dpt_temporal.py:75-76,80-87) over self.BT = batch * T frames.  Returns path_3 (padded at the layer_2 size)."""
+        (dpt_temporal.py:75-76,80-87) over self.BT = batch * T frames.  Returns path_3 (padded at the layer_2 size), or with
+        split_mm3 the inputs of motion module 3's per-frame part (att, h, x; dense at the layer_2 size) -- the streaming mode
+        finishes that module only for the frames it predicts."""
         pw = self.pw
         ph, pwid, F, oc = self.ph, self.pw_, pw.features, pw.oc
         BT = self.BT
@@ -482,6 +504,9 @@ class ForwardPlan:
             self._motion_module(2, p4d, (h3, w3), F, p4, L.MAP_PADDED)
         p3d = self.buf("path_3d", BT * h2 * w2, F)
         self._fusion(3, p4, None, rn3, rn3_relu, h3, w3, h2, w2, p3d, L.MAP_SAME)
+        if split_mm3:
+            att, hbuf = self._mm_front(3, p3d, (h2, w2), F)
+            return att, hbuf, p3d
         p3 = self.padded("path_3", h2, w2, F)
         self._motion_module(3, p3d, (h2, w2), F, p3, L.MAP_PADDED)
         return p3
@@ -641,8 +666,11 @@ class StreamPlan(ForwardPlan):
         ctx = self.idx[self.IDX_CTX].data_ptr()
         self.op(lib.vda_copy_frames, self.rings[2].data_ptr(), l3.data_ptr(), ctx, None, T, self.frame_bytes[2])
         self.op(lib.vda_copy_frames, self.rings[3].data_ptr(), l4.data_ptr(), ctx, None, T, self.frame_bytes[3])
-        p3 = self._head_middle(l3, l4, skip_tmp_block)
-        p3_bytes = (h2 + 2) * (w2 + 2) * F * esz
+        # motion module 3 is cut after its last temporal attention: what follows (output projection, feed-forward,
+        # proj_out, residual) is per frame and only the predicted frames' path_3 is ever read (dpt_temporal.py:222-227),
+        # so the tails finish it on their n frames instead of the middle stage on all T -- the same per-frame arithmetic
+        mm3_parts = self._head_middle(l3, l4, skip_tmp_block, split_mm3=True)
+        mm3_bytes = h2 * w2 * F * esz
         self._end_stage("middle")
 
         # ---- tails: the frames that get a depth map (dpt_temporal.py:187-192,222-227)
@@ -655,7 +683,13 @@ class StreamPlan(ForwardPlan):
             pred = self.idx[self.IDX_PRED].data_ptr()
             self.op(lib.vda_copy_frames, self.rings[0].data_ptr(), l1.data_ptr(), pred, None, n, self.frame_bytes[0])
             self.op(lib.vda_copy_frames, self.rings[1].data_ptr(), l2.data_ptr(), pred, None, n, self.frame_bytes[1])
-            self.op(lib.vda_copy_frames, p3.data_ptr(), p3s.data_ptr(), self.idx[self.IDX_P3].data_ptr(), None, n, p3_bytes)
+            parts = []
+            for k, src_buf in enumerate(mm3_parts):
+                dst_buf = self.buf(f"mm3in{k}", n * h2 * w2, F)
+                self.op(lib.vda_copy_frames, src_buf.data_ptr(), dst_buf.data_ptr(), self.idx[self.IDX_P3].data_ptr(), None, n,
+                        mm3_bytes)
+                parts.append(dst_buf)
+            self._mm_back(3, parts[0], parts[1], parts[2], (h2, w2), F, p3s, L.MAP_PADDED)
             self.depths[n] = self._head_tail(p3s, l1, l2)
             self._end_stage(f"tail{n}")
 
