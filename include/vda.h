@@ -241,6 +241,17 @@ int vda_scale_apply(const float* in, float* out, const float* st, int64_t count,
 int vda_copy_frames(const void* src, void* dst, const int32_t* src_idx, const int32_t* dst_idx, int32_t n,
                     int64_t frame_bytes, vda_stream_t stream);
 
+/* Depth visualisation of `save_video(..., is_depths=True)` (utils/dc_utils.py:70-86), SURVEY section 8f rank 2.
+ * vda_depth_minmax: minmax[0], minmax[1] = min, max over `count` f32 values (`frames.min(), frames.max()`, :74);
+ * `partial` is caller-provided scratch of vda_depth_minmax_workspace_floats() floats.
+ * vda_depth_vis: u = trunc((depth - min) / (max - min) * 255) in f32 arithmetic like numpy (:77, bit-identical; 0 when
+ * max == min, where numpy casts a NaN); out[i] = u (lut == NULL: `grayscale=True`, 1 byte per pixel) or
+ * out[3i..3i+2] = lut[3u..3u+2] (lut = DEVICE uint8[256][3], the caller's `(colormap * 255).astype(uint8)`: :78-81). */
+int64_t vda_depth_minmax_workspace_floats(void);
+int vda_depth_minmax(const float* depth, int64_t count, float* partial, float* minmax, vda_stream_t stream);
+int vda_depth_vis(const float* depth, int64_t count, const float* minmax, const uint8_t* lut, uint8_t* out,
+                  vda_stream_t stream);
+
 /* 8-frame linear cross-fade (utils/util.py:65-74, video_depth.py:397-402):
  * inout[i] = inout[i]*(1-w_i) + max(post[i]*st[0]+st[1], 0)*w_i, w = i/(n-1). */
 int vda_blend(float* inout, const float* post, const float* st, int32_t n, int64_t frame_elems, vda_stream_t stream);

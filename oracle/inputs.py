@@ -44,3 +44,33 @@ def synthetic_eval_case(seed: int, n: int = 3, h: int = 40, w: int = 56):
     valid &= gt > 0   # the reference's metrics divide by the ground truth of every valid pixel
     pred = (3.0 / np.maximum(gt, 0.5) + 0.2 + 0.02 * rng.standard_normal((n, h, w))).astype(np.float32)
     return pred, gt, valid
+
+
+def synthetic_depths(seed: int, n: int, h: int, w: int, signed: bool = False) -> np.ndarray:
+    """float32 [n, h, w] depth stack for the visualisation tests: smooth ramps plus noise over about two decades;
+    `signed` adds negative values (the streaming mode's aligned depths are not clamped, video_depth.py:313)."""
+    rng = np.random.default_rng(3000 + seed)
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    d = np.stack([0.05 + 4.0 * ((xx / w + 0.3 * i) % 1.0) * (0.2 + yy / h) for i in range(n)])
+    d = d * (1.0 + 0.1 * rng.standard_normal(d.shape)) + (-0.3 if signed else 0.0)
+    return (d if signed else np.abs(d)).astype(np.float32)
+
+
+def synthetic_colour_tables(seed: int):
+    """Stand-ins for matplotlib's tables (not in the image): (inferno-like float64 [256, 3], Spectral-like float64 [256, 4]),
+    values in [0, 1] including exact 0 and 1 entries."""
+    rng = np.random.default_rng(4000 + seed)
+    a, b = rng.random((256, 3)), rng.random((256, 4))
+    a[0], a[255], b[0], b[255] = 0.0, 1.0, 1.0, 0.0
+    return a, b
+
+
+def synthetic_clip_file(path: str, n: int = 24, h: int = 48, w: int = 64, fps: float = 30.0):
+    """Writes the small test clip (moving colour gradients, mp4v) with cv2 -- the same codec stack reads it back."""
+    import cv2
+    wr = cv2.VideoWriter(path, cv2.VideoWriter_fourcc(*"mp4v"), fps, (w, h))
+    assert wr.isOpened(), path
+    yy, xx = np.mgrid[0:h, 0:w]
+    for i in range(n):
+        wr.write(np.stack([(xx * 4 + i * 5) % 256, (yy * 5 + i * 3) % 256, ((xx + yy) * 2 + i * 7) % 256], -1).astype(np.uint8))
+    wr.release()

@@ -216,6 +216,87 @@ def eval_cases():
     eval_case("s2_d40", 2, 40.0)
 
 
+IO_READ_CASES = [(-1, -1, -1), (10, -1, -1), (-1, 10, -1), (17, 12, 40), (-1, 100, -1), (5, -1, 32)]
+IO_DEPTH_CASES = [("odd", 11, 5, 37, 41, False), ("vec", 12, 3, 32, 48, True)]
+
+
+def io_cases():
+    """`make_goldens.py --io`: the REAL `read_video_frames` / `save_video` (utils/dc_utils.py) vs oracle/video_io.py.
+    dc_utils imports imageio and matplotlib.cm at module level; neither is in the image.  The stubs below do no arithmetic
+    of the path: imageio's writer records the pictures it is handed, matplotlib.cm serves injected colour tables."""
+    import hashlib
+    from oracle import video_io as oio
+    from oracle.inputs import synthetic_clip_file, synthetic_colour_tables, synthetic_depths
+    inferno, spectral = synthetic_colour_tables(0)
+    recorded = []
+
+    class Writer:
+        def __init__(self, path, **kw):
+            recorded.append({"path": path, "kw": kw, "frames": []})
+
+        def append_data(self, a):
+            recorded[-1]["frames"].append(np.array(a))
+
+        def close(self):
+            pass
+
+    imageio = types.ModuleType("imageio")
+    imageio.get_writer = Writer
+    mpl, cm = types.ModuleType("matplotlib"), types.ModuleType("matplotlib.cm")
+
+    class Inferno:
+        colors = inferno.tolist()
+
+    cm.get_cmap = lambda name: {"inferno": Inferno}[name]
+    cm.Spectral = lambda u: spectral[u]
+    mpl.cm = cm
+    sys.modules.update({"imageio": imageio, "matplotlib": mpl, "matplotlib.cm": cm})
+    sys.modules.pop("decord", None)
+    from utils import dc_utils as ref
+    assert not ref.DECORD_AVAILABLE
+
+    clip = os.path.join(GOLD, "clip_48x64.mp4")
+    if not os.path.exists(clip):
+        synthetic_clip_file(clip)
+    out = {}
+    for k, (plen, tfps, mres) in enumerate(IO_READ_CASES):
+        rf, rfps = ref.read_video_frames(clip, plen, tfps, mres)
+        of, ofps = oio.read_video_frames(clip, plen, tfps, mres)
+        assert rf.dtype == np.uint8 and np.array_equal(rf, of) and rfps == ofps, (plen, tfps, mres)
+        out[f"read{k}_args"] = np.array([plen, tfps, mres], dtype=np.float64)
+        out[f"read{k}_shape_fps"] = np.array(list(rf.shape) + [rfps], dtype=np.float64)
+        out[f"read{k}_sha"] = np.frombuffer(hashlib.sha256(np.ascontiguousarray(rf).tobytes()).digest(), dtype=np.uint8)
+        out[f"read{k}_first"] = rf[0]
+        print(f"read_video_frames{(plen, tfps, mres)}: {rf.shape} fps {rfps}: oracle == reference")
+    try:
+        ref.read_video_frames(os.path.join(GOLD, "no_such_file.mp4"), -1, 24, -1)
+        raise SystemExit("expected ValueError")
+    except ValueError as e:
+        manifest["read_video_missing_file_error"] = f"ValueError: {e}"
+    for name, seed, n, h, w, signed in IO_DEPTH_CASES:
+        d = synthetic_depths(seed, n, h, w, signed)
+        for mode, kw in (("grey", dict(grayscale=True)), ("inferno", dict()), ("spectral", dict(spectral=True)),
+                         ("spectral_grey", dict(grayscale=True, spectral=True))):
+            ref.save_video(d, "unused.mp4", fps=12, is_depths=True, **kw)
+            pics = np.stack(recorded[-1]["frames"])
+            ora = oio.depth_pictures(d, inferno=inferno, spectral_table=spectral, **kw)
+            assert pics.dtype == np.uint8 and np.array_equal(pics, ora), (name, mode)
+            out[f"depth_{name}_{mode}"] = pics
+        print(f"save_video depth pictures {name} {d.shape}: oracle == reference in 4 modes; writer kwargs {recorded[-1]['kw']}")
+    frames = synthetic_video(3, 16, 24, 5)
+    ref.save_video(frames, "unused.mp4", fps=7)
+    assert np.array_equal(np.stack(recorded[-1]["frames"]), frames)  # plain frames go to the writer untouched
+    np.savez_compressed(os.path.join(GOLD, "video_io.npz"), **out)
+    manifest["cases"]["video_io"] = {"clip": "clip_48x64.mp4", "read_cases": IO_READ_CASES,
+                                     "depth_cases": [c[0] for c in IO_DEPTH_CASES], "writer_kwargs": str(recorded[-1]["kw"])}
+    with open(os.path.join(GOLD, "MANIFEST.json")) as f:
+        old = json.load(f)
+    old["cases"].update(manifest["cases"])
+    old["read_video_missing_file_error"] = manifest["read_video_missing_file_error"]
+    with open(os.path.join(GOLD, "MANIFEST.json"), "w") as f:
+        json.dump(old, f, indent=1)
+
+
 def main_new_only():
     """`make_goldens.py --new`: only the cases added after the first golden set (merged into MANIFEST.json)."""
     with open(os.path.join(GOLD, "MANIFEST.json")) as f:
@@ -230,6 +311,9 @@ def main_new_only():
 
 
 if __name__ == "__main__":
+    if "--io" in sys.argv:
+        io_cases()
+        sys.exit(0)
     if "--new" in sys.argv:
         main_new_only()
         sys.exit(0)

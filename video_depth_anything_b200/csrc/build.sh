@@ -8,7 +8,7 @@ mkdir -p "$OBJ"
 NVCC="${NVCC:-nvcc}"
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -fvisibility=default)
 pids=()
-for f in api gemm_simt gemm_tc gemm_tc2 conv_tc attn_simt attn_tc head_tail norms resize driver_kernels; do
+for f in api gemm_simt gemm_tc gemm_tc2 conv_tc attn_simt attn_tc head_tail norms resize driver_kernels vis; do
   if [ ! -f "$OBJ/$f.o" ] || [ "$HERE/$f.cu" -nt "$OBJ/$f.o" ] || [ -n "$(find "$HERE" -maxdepth 1 \( -name '*.cuh' -o -name '*.h' \) -newer "$OBJ/$f.o" 2>/dev/null)" ] || [ "$HERE/../../include/vda.h" -nt "$OBJ/$f.o" ]; then
     "$NVCC" "${FLAGS[@]}" -c "$HERE/$f.cu" -o "$OBJ/$f.o" &
     pids+=($!)
