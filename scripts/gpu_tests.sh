@@ -17,6 +17,7 @@ run tc_attn 300 tests/test_gpu_tc.py::test_flash_attention_tc
 run fwd_fp32 900 tests/test_gpu_forward.py -k "(fp32 or taps or contract) and not driver"
 run fwd_bf16 900 tests/test_gpu_forward.py -k "bf16 and not driver"
 run driver 600 tests/test_gpu_forward.py -k "driver"
+run video_io 300 tests/test_video_io.py
 run fwd_misc 600 tests/test_gpu_forward.py -k "not fp32 and not taps and not contract and not bf16 and not driver"
 timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "== smoke rc=$? $(tail -1 gpurun_out/smoke.log)"
 timeout 900 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.log 2>&1; echo "== bench rc=$? $(tail -c 1500 gpurun_out/bench.log)"

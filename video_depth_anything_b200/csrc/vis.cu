@@ -80,18 +80,28 @@ __global__ void __launch_bounds__(256) depth_vis_kernel(const float* __restrict_
   }
   const float mn = minmax[0], range = __fsub_rn(minmax[1], minmax[0]);
   const long long n4 = vec ? n >> 2 : 0;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
-    const float4 v = reinterpret_cast<const float4*>(d)[i];
-    const uint32_t a = norm_u8(v.x, mn, range), b = norm_u8(v.y, mn, range), c = norm_u8(v.z, mn, range),
-                   e = norm_u8(v.w, mn, range);
-    if (!COLOUR) {
-      reinterpret_cast<uint32_t*>(out)[i] = a | (b << 8) | (c << 16) | (e << 24);
-    } else {
-      const uint32_t A = slut[a], B = slut[b], Cc = slut[c], E = slut[e];  // 0x00BBGGRR each
-      uint32_t* o = reinterpret_cast<uint32_t*>(out) + 3 * i;             // 12 bytes: R G B R | G B R G | B R G B
-      o[0] = A | (B << 24);
-      o[1] = (B >> 8) | (Cc << 16);
-      o[2] = (Cc >> 16) | (E << 8);
+  // two float4 loads in flight per thread (the loop body is ~80 instructions of IEEE division behind each load)
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n4; i0 += 2 * stride) {
+    float4 v[2];
+    v[0] = reinterpret_cast<const float4*>(d)[i0];
+    const bool two = i0 + stride < n4;
+    if (two) v[1] = reinterpret_cast<const float4*>(d)[i0 + stride];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+      const long long i = i0 + u * stride;
+      const uint32_t a = norm_u8(v[u].x, mn, range), b = norm_u8(v[u].y, mn, range), c = norm_u8(v[u].z, mn, range),
+                     e = norm_u8(v[u].w, mn, range);
+      if (!COLOUR) {
+        reinterpret_cast<uint32_t*>(out)[i] = a | (b << 8) | (c << 16) | (e << 24);
+      } else {
+        const uint32_t A = slut[a], B = slut[b], Cc = slut[c], E = slut[e];  // 0x00BBGGRR each
+        uint32_t* o = reinterpret_cast<uint32_t*>(out) + 3 * i;             // 12 bytes: R G B R | G B R G | B R G B
+        o[0] = A | (B << 24);
+        o[1] = (B >> 8) | (Cc << 16);
+        o[2] = (Cc >> 16) | (E << 8);
+      }
     }
   }
   for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
