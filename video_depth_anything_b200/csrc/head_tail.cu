@@ -13,10 +13,14 @@
 //
 // Work decomposition: a CTA owns groups of 8 consecutive tiles (8 accumulators of 32 TMEM columns, double-buffered);
 // the channel dimension is walked in chunks of 32 so that one chunk of the weights (9 taps x 32 x 32 fp32 = 36 KB, TMA,
-// 128B swizzle) serves all 8 tiles.  Roles: warps 0-7 interpolate (4 teams of 2 warps, one smem buffer per team),
-// warp 8 loads weights, warp 9 issues MMAs, warps 10-13 run the epilogue (bias, ReLU, 32->1 dot, ReLU, store).
-// Measured (ncu, vitl 518x518): 3.0 ms vs 8.4 ms for the unfused upsample + conv; it is bound by the rate of the
-// 144 small (128x32x8) MMAs per tile (~85 clk each), not by the producers or by operand alignment (both tested).
+// 128B swizzle) serves all 8 tiles.  Roles: warps 0-15 interpolate (4 teams of 4 warps, one smem buffer per team),
+// warp 16 loads weights, warp 17 issues MMAs, warps 18-21 run the epilogue (bias, ReLU, 32->1 dot, ReLU, store).
+// Measured (vitl 518x518): TF32 operands 3.0 ms vs 8.4 ms for the unfused upsample + conv; fp16 operands (half the MMAs)
+// 2.32 ms, where ncu's instruction sampling showed the MMA issuer waiting on the producers 45 % of its time and the
+// producers on their global loads (27 %) and on free buffers (22 %): a latency-bound hand-off.  Column-walking producers
+// with shared horizontal interpolation (0.82 G instead of 1.31 G warp instructions) gave 2.25 ms with 8 producer warps,
+// 1.78 ms with 12 and 1.70 ms with 16 (80 registers per thread, 176 B of spills in the epilogue role).  The tensor pipe is
+// busy 2.14 M clk per SM (~65 clk per 128x32x16 MMA), i.e. the MMA-bound floor is ~1.2 ms.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tmap.h"
@@ -40,7 +44,7 @@ constexpr int OFF_A = NBBUF * BBUF;
 constexpr int OFF_PAR = OFF_A + NABUF * ABUF;  // bias[32], head_w[32]
 constexpr int OFF_BAR = OFF_PAR + 256;
 constexpr int HT_SMEM = OFF_BAR + 256;
-constexpr int NPROD_WARPS = 8;
+constexpr int NPROD_WARPS = 16;
 constexpr int NTEAMS = NABUF;                          // producer team k fills buffer k: fills proceed concurrently
 constexpr int TEAM_WARPS = NPROD_WARPS / NTEAMS;
 constexpr int TEAM_THREADS = TEAM_WARPS * 32;
@@ -138,67 +142,85 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
           const int f = T / tiles_per_frame, rem = T % tiles_per_frame;
           const int ty0 = (rem / a.tiles_x) * TH, tx0 = (rem % a.tiles_x) * TW;
           uint8_t* abuf = smem + OFF_A + ab * ABUF;
-          // (pixel, 8-channel group) items in batches of NIT per thread; the 4*NIT corner loads of a batch are issued
-          // before any arithmetic so that their latencies overlap
-          constexpr int NITEMS = HP * (KC / 8), NIT = 4;
-          for (int it0 = tt; it0 < NITEMS; it0 += NIT * TEAM_THREADS) {
-          uint4 raw[NIT][4];
-          float wts[NIT][4];
-          int dsto[NIT];
-#pragma unroll
-          for (int j = 0; j < NIT; ++j) {
-            const int it = it0 + j * TEAM_THREADS;
-            dsto[j] = -1;
-            wts[j][0] = wts[j][1] = wts[j][2] = wts[j][3] = 0.f;
-            raw[j][0] = raw[j][1] = raw[j][2] = raw[j][3] = make_uint4(0, 0, 0, 0);
-            if (it < NITEMS) {
-              const int p = it / (KC / 8), cg = it % (KC / 8);
-              const int hy = p / PW, hx = p - hy * PW;
-              const int oy = ty0 + hy - 1, ox = tx0 + hx - 1;
-              dsto[j] = (H ? cg : 2 * cg) * SLAB + p * 16;
-              if (oy >= 0 && oy < a.oh && ox >= 0 && ox < a.ow) {
-                const float h1r = a.rh * oy;
-                const int h1 = (int)h1r;
-                const int h1p = (h1 < a.ih - 1) ? 1 : 0;
-                const float h1l = h1r - h1;
-                const float w1r = a.rw * ox;
-                const int w1 = (int)w1r;
-                const int w1p = (w1 < a.iw - 1) ? 1 : 0;
-                const float w1l = w1r - w1;
-                wts[j][0] = 1.f - h1l; wts[j][1] = h1l; wts[j][2] = 1.f - w1l; wts[j][3] = w1l;
-                const bf16* base = a.x + (((long long)f * a.ih + h1) * a.iw + w1) * a.C + kc * KC + cg * 8;
-                raw[j][0] = *reinterpret_cast<const uint4*>(base);
-                raw[j][1] = *reinterpret_cast<const uint4*>(base + (long long)w1p * a.C);
-                raw[j][2] = *reinterpret_cast<const uint4*>(base + (long long)h1p * a.iw * a.C);
-                raw[j][3] = *reinterpret_cast<const uint4*>(base + ((long long)h1p * a.iw + w1p) * a.C);
-              }
-            }
-          }
-#pragma unroll
-          for (int j = 0; j < NIT; ++j) {
-            if (dsto[j] < 0) continue;
-            const float h0l = wts[j][0], h1l = wts[j][1], w0l = wts[j][2], w1l = wts[j][3];
-            const uint32_t* ra = reinterpret_cast<const uint32_t*>(&raw[j][0]);
-            const uint32_t* rb = reinterpret_cast<const uint32_t*>(&raw[j][1]);
-            const uint32_t* rc = reinterpret_cast<const uint32_t*>(&raw[j][2]);
-            const uint32_t* rd = reinterpret_cast<const uint32_t*>(&raw[j][3]);
-            float o[8];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {  // zero weights + zero data give the conv's zero padding outside the image
-              o[2 * i] = h0l * (w0l * bf16lo_to_f32(ra[i]) + w1l * bf16lo_to_f32(rb[i])) +
-                         h1l * (w0l * bf16lo_to_f32(rc[i]) + w1l * bf16lo_to_f32(rd[i]));
-              o[2 * i + 1] = h0l * (w0l * bf16hi_to_f32(ra[i]) + w1l * bf16hi_to_f32(rb[i])) +
-                             h1l * (w0l * bf16hi_to_f32(rc[i]) + w1l * bf16hi_to_f32(rd[i]));
-            }
-            uint8_t* dst = abuf + dsto[j];
-            if (H) {
-              *reinterpret_cast<uint4*>(dst) = make_uint4(pack_f16x2_sat(o[0], o[1]), pack_f16x2_sat(o[2], o[3]),
+          // A task = one halo column (hx) x one 8-channel group x one segment of SEGR halo rows, walked top to bottom.
+          // The horizontal interpolation w0*a + w1*b of an INPUT row is computed once and shared by the output rows that
+          // use it (1.75x upsampling: ~0.57 new input rows per output row), and the next input row's two loads are in
+          // flight while the current pair's output rows are emitted.  The item-per-(pixel, group) form before this
+          // fetched and unpacked four corners per item: 27 instructions per interpolated element, 1.31 G warp
+          // instructions per launch at 53 % issue utilisation with two producer warps per scheduler (ncu) -- the
+          // producers, not the MMAs, set the pace.
+          constexpr int NCG = KC / 8, SEG = 2, SEGR = (TH + 2) / SEG, NTASK = SEG * PW * NCG;
+          for (int task = tt; task < NTASK; task += TEAM_THREADS) {
+            const int cg = task % NCG, r1 = task / NCG;
+            const int hx = r1 % PW, hy0 = (r1 / PW) * SEGR;
+            const int ox = tx0 + hx - 1, oy_lo = ty0 + hy0 - 1;  // output pixel of the segment's first halo row
+            uint8_t* dst = abuf + (H ? cg : 2 * cg) * SLAB + (hy0 * PW + hx) * 16;
+            auto put = [&](int r, const float* o) {
+              uint8_t* d = dst + r * (PW * 16);
+              if (H) {
+                *reinterpret_cast<uint4*>(d) = make_uint4(pack_f16x2_sat(o[0], o[1]), pack_f16x2_sat(o[2], o[3]),
                                                           pack_f16x2_sat(o[4], o[5]), pack_f16x2_sat(o[6], o[7]));
-            } else {
-              *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
-              *reinterpret_cast<float4*>(dst + SLAB) = make_float4(o[4], o[5], o[6], o[7]);
+              } else {
+                *reinterpret_cast<float4*>(d) = make_float4(o[0], o[1], o[2], o[3]);
+                *reinterpret_cast<float4*>(d + SLAB) = make_float4(o[4], o[5], o[6], o[7]);
+              }
+            };
+            // halo rows outside the image are the convolution's zero padding
+            int rA = max(0, -oy_lo), rB = min(SEGR, a.oh - oy_lo);
+            if (ox < 0 || ox >= a.ow) rA = rB = 0;
+            {
+              const float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+              for (int r = 0; r < SEGR; ++r)
+                if (r < rA || r >= rB) put(r, z);
             }
-          }
+            if (rA >= rB) continue;
+            const float w1r = a.rw * ox;
+            const int w1 = (int)w1r;
+            const float w1l = w1r - w1, w0l = 1.f - w1l;
+            const int step = (w1 < a.iw - 1) ? a.C : 0;
+            const long long rowpitch = (long long)a.iw * a.C;
+            int k = (int)(a.rh * (oy_lo + rA));  // first input row
+            const bf16* src = a.x + ((long long)f * a.ih + k) * rowpitch + (long long)w1 * a.C + kc * KC + cg * 8;
+            uint4 ra = *reinterpret_cast<const uint4*>(src), rb = *reinterpret_cast<const uint4*>(src + step);
+            float prev[8], cur[8], o[8];
+            bool have_prev = false;
+            for (int r = rA;; ++k) {
+              {
+                const uint32_t* pa = reinterpret_cast<const uint32_t*>(&ra);
+                const uint32_t* pb = reinterpret_cast<const uint32_t*>(&rb);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  cur[2 * i] = w0l * bf16lo_to_f32(pa[i]) + w1l * bf16lo_to_f32(pb[i]);
+                  cur[2 * i + 1] = w0l * bf16hi_to_f32(pa[i]) + w1l * bf16hi_to_f32(pb[i]);
+                }
+              }
+              const bool more = k < a.ih - 1;
+              if (more) {  // next input row in flight while this pair's rows are emitted (unused once, at the segment's end)
+                src += rowpitch;
+                ra = *reinterpret_cast<const uint4*>(src);
+                rb = *reinterpret_cast<const uint4*>(src + step);
+              }
+              while (r < rB) {
+                const float h1r = a.rh * (oy_lo + r);
+                const int h1 = (int)h1r;
+                const float h1l = h1r - h1, h0l = 1.f - h1l;
+                if (h1 == k - 1 && have_prev) {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) o[i] = h0l * prev[i] + h1l * cur[i];
+                } else if (h1 == k && !more) {  // bottom edge: both rows of the pair are the last input row
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) o[i] = h0l * cur[i] + h1l * cur[i];
+                } else {
+                  break;
+                }
+                put(r, o);
+                ++r;
+              }
+              if (r >= rB) break;
+#pragma unroll
+              for (int i = 0; i < 8; ++i) prev[i] = cur[i];
+              have_prev = true;
+            }
           }
           ptx::fence_proxy_async();
           __syncwarp();
