@@ -19,7 +19,8 @@
 // 2.32 ms, where ncu's instruction sampling showed the MMA issuer waiting on the producers 45 % of its time and the
 // producers on their global loads (27 %) and on free buffers (22 %): a latency-bound hand-off.  Column-walking producers
 // with shared horizontal interpolation (0.82 G instead of 1.31 G warp instructions) gave 2.25 ms with 8 producer warps,
-// 1.78 ms with 12 and 1.70 ms with 16 (80 registers per thread, 176 B of spills in the epilogue role).  The tensor pipe is
+// 1.78 ms with 12 and 1.70 ms with 16 (80 registers per thread, 176 B of spills in the epilogue role), 1.65 ms with the
+// multiply-adds as packed fp32 pairs (FMUL2 / FFMA2).  The tensor pipe is
 // busy 2.14 M clk per SM (~65 clk per 128x32x16 MMA), i.e. the MMA-bound floor is ~1.2 ms.
 #include "common.cuh"
 #include "ptx.cuh"
@@ -155,8 +156,11 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
             const int hx = r1 % PW, hy0 = (r1 / PW) * SEGR;
             const int ox = tx0 + hx - 1, oy_lo = ty0 + hy0 - 1;  // output pixel of the segment's first halo row
             uint8_t* dst = abuf + (H ? cg : 2 * cg) * SLAB + (hy0 * PW + hx) * 16;
-            auto put = [&](int r, const float* o) {
+            auto put = [&](int r, const uint64_t* o2) {  // o2[i] = channels (2i, 2i+1)
               uint8_t* d = dst + r * (PW * 16);
+              float o[8];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) upk2(o2[i], o[2 * i], o[2 * i + 1]);
               if (H) {
                 *reinterpret_cast<uint4*>(d) = make_uint4(pack_f16x2_sat(o[0], o[1]), pack_f16x2_sat(o[2], o[3]),
                                                           pack_f16x2_sat(o[4], o[5]), pack_f16x2_sat(o[6], o[7]));
@@ -169,7 +173,7 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
             int rA = max(0, -oy_lo), rB = min(SEGR, a.oh - oy_lo);
             if (ox < 0 || ox >= a.ow) rA = rB = 0;
             {
-              const float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+              const uint64_t z[4] = {0ull, 0ull, 0ull, 0ull};
               for (int r = 0; r < SEGR; ++r)
                 if (r < rA || r >= rB) put(r, z);
             }
@@ -177,22 +181,22 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
             const float w1r = a.rw * ox;
             const int w1 = (int)w1r;
             const float w1l = w1r - w1, w0l = 1.f - w1l;
+            const uint64_t w1l2 = pk2(w1l, w1l), w0l2 = pk2(w0l, w0l);
             const int step = (w1 < a.iw - 1) ? a.C : 0;
             const long long rowpitch = (long long)a.iw * a.C;
             int k = (int)(a.rh * (oy_lo + rA));  // first input row
             const bf16* src = a.x + ((long long)f * a.ih + k) * rowpitch + (long long)w1 * a.C + kc * KC + cg * 8;
             uint4 ra = *reinterpret_cast<const uint4*>(src), rb = *reinterpret_cast<const uint4*>(src + step);
-            float prev[8], cur[8], o[8];
+            uint64_t prev[4], cur[4], o[4];
             bool have_prev = false;
             for (int r = rA;; ++k) {
               {
                 const uint32_t* pa = reinterpret_cast<const uint32_t*>(&ra);
                 const uint32_t* pb = reinterpret_cast<const uint32_t*>(&rb);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  cur[2 * i] = w0l * bf16lo_to_f32(pa[i]) + w1l * bf16lo_to_f32(pb[i]);
-                  cur[2 * i + 1] = w0l * bf16hi_to_f32(pa[i]) + w1l * bf16hi_to_f32(pb[i]);
-                }
+                for (int i = 0; i < 4; ++i)
+                  cur[i] = fma2(w1l2, pk2(bf16lo_to_f32(pb[i]), bf16hi_to_f32(pb[i])),
+                                mul2(w0l2, pk2(bf16lo_to_f32(pa[i]), bf16hi_to_f32(pa[i]))));
               }
               const bool more = k < a.ih - 1;
               if (more) {  // next input row in flight while this pair's rows are emitted (unused once, at the segment's end)
@@ -204,12 +208,13 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
                 const float h1r = a.rh * (oy_lo + r);
                 const int h1 = (int)h1r;
                 const float h1l = h1r - h1, h0l = 1.f - h1l;
+                const uint64_t h1l2 = pk2(h1l, h1l), h0l2 = pk2(h0l, h0l);
                 if (h1 == k - 1 && have_prev) {
 #pragma unroll
-                  for (int i = 0; i < 8; ++i) o[i] = h0l * prev[i] + h1l * cur[i];
+                  for (int i = 0; i < 4; ++i) o[i] = fma2(h1l2, cur[i], mul2(h0l2, prev[i]));
                 } else if (h1 == k && !more) {  // bottom edge: both rows of the pair are the last input row
 #pragma unroll
-                  for (int i = 0; i < 8; ++i) o[i] = h0l * cur[i] + h1l * cur[i];
+                  for (int i = 0; i < 4; ++i) o[i] = fma2(h1l2, cur[i], mul2(h0l2, cur[i]));
                 } else {
                   break;
                 }
@@ -218,7 +223,7 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
               }
               if (r >= rB) break;
 #pragma unroll
-              for (int i = 0; i < 8; ++i) prev[i] = cur[i];
+              for (int i = 0; i < 4; ++i) prev[i] = cur[i];
               have_prev = true;
             }
           }

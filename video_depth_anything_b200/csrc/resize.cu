@@ -32,7 +32,10 @@ __global__ void __launch_bounds__(256) bilinear_kernel(const T* __restrict__ in,
   TO* ocol = out + (((long long)f * OH + opad) * OW + ox + opad) * C + cv * 8;
   const long long irow = (long long)IW * C, orow = (long long)OW * C;
   const int step = w1p * C;
-  float tp[8], bt[8], a[8], b[8], o[8];
+  // channel pairs as packed fp32 (FMUL2 / FFMA2: half the issue slots of the sixteen multiply-adds per row)
+  uint64_t tp[4], bt[4];
+  float a[8], b[8], o[8];
+  const uint64_t w0l2 = pk2(w0l, w0l), w1l2 = pk2(w1l, w1l);
   int top = -2, bot = -2;  // input rows whose horizontal interpolation sits in tp and bt
   const int oy0 = blockIdx.y * rows, oy1 = min(oy0 + rows, oh);
   for (int oy = oy0; oy < oy1; ++oy) {
@@ -43,31 +46,32 @@ __global__ void __launch_bounds__(256) bilinear_kernel(const T* __restrict__ in,
     if (h1 != top) {
       if (h1 == bot) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) tp[i] = bt[i];
+        for (int i = 0; i < 4; ++i) tp[i] = bt[i];
       } else {
         const T* p = col + h1 * irow;
         Vec8<T>::load(p, a);
         Vec8<T>::load(p + step, b);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) tp[i] = w0l * a[i] + w1l * b[i];
+        for (int i = 0; i < 4; ++i) tp[i] = fma2(w1l2, pk2(b[2 * i], b[2 * i + 1]), mul2(w0l2, pk2(a[2 * i], a[2 * i + 1])));
       }
       top = h1;
     }
     if (h1b != bot) {
       if (h1b == top) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) bt[i] = tp[i];
+        for (int i = 0; i < 4; ++i) bt[i] = tp[i];
       } else {
         const T* p = col + h1b * irow;
         Vec8<T>::load(p, a);
         Vec8<T>::load(p + step, b);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) bt[i] = w0l * a[i] + w1l * b[i];
+        for (int i = 0; i < 4; ++i) bt[i] = fma2(w1l2, pk2(b[2 * i], b[2 * i + 1]), mul2(w0l2, pk2(a[2 * i], a[2 * i + 1])));
       }
       bot = h1b;
     }
+    const uint64_t h0l2 = pk2(h0l, h0l), h1l2 = pk2(h1l, h1l);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) o[i] = h0l * tp[i] + h1l * bt[i];
+    for (int i = 0; i < 4; ++i) upk2(fma2(h1l2, bt[i], mul2(h0l2, tp[i])), o[2 * i], o[2 * i + 1]);
     Vec8<TO>::store(ocol + oy * orow, o);
   }
 }
