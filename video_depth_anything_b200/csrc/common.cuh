@@ -76,6 +76,29 @@ __device__ __forceinline__ float gelu_fast(float x) {
   return fmaf(-ax, h, fmaxf(x, 0.f));
 }
 
+// Two GELUs at once with the FMA-pipe work as packed fp32 pairs (FMUL2 / FFMA2): the same operations in the same order
+// as gelu_fast on each element (bit-identical results), ~8 instead of 13 issue slots per element.
+__device__ __forceinline__ void gelu_fast2(float x0, float x1, float& o0, float& o1) {
+  const float a0 = fabsf(x0), a1 = fabsf(x1);
+  const uint64_t ax = pk2(a0, a1), x = pk2(x0, x1);
+  float u0, u1, t0, t1, z0, z1, e0, e1;
+  constexpr float K = 0.3275911f * 0.70710678118654752440f;
+  upk2(fma2(pk2(K, K), ax, pk2(1.0f, 1.0f)), u0, u1);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(u0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(u1));
+  const uint64_t t = pk2(t0, t1);
+  uint64_t p = fma2(t, pk2(0.5f * 1.061405429f, 0.5f * 1.061405429f), pk2(0.5f * -1.453152027f, 0.5f * -1.453152027f));
+  p = fma2(t, p, pk2(0.5f * 1.421413741f, 0.5f * 1.421413741f));
+  p = fma2(t, p, pk2(0.5f * -0.284496736f, 0.5f * -0.284496736f));
+  p = fma2(t, p, pk2(0.5f * 0.254829592f, 0.5f * 0.254829592f));
+  const uint64_t y = mul2(x, pk2(0.84932180028801904272f, 0.84932180028801904272f));
+  upk2(mul2(y, y), z0, z1);
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(-z0));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(-z1));
+  const uint64_t h = mul2(mul2(t, p), pk2(e0, e1));
+  upk2(fma2(pk2(-a0, -a1), h, pk2(fmaxf(x0, 0.f), fmaxf(x1, 0.f))), o0, o1);
+}
+
 template <typename T> __device__ __forceinline__ float to_f32(T v);
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ float to_f32<bf16>(bf16 v) { return __bfloat162float(v); }

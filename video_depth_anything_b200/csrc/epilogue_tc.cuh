@@ -135,7 +135,9 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
         for (int k = 0; k < 4; k += 2) {
           const uint32_t vr = pack_bf16x2(v[i + k] + bb[k], v[i + k + 1] + bb[k + 1]);
           const uint32_t gr = pack_bf16x2(g[i + k] + gb[k], g[i + k + 1] + gb[k + 1]);
-          const uint32_t ar = pack_bf16x2(gelu_fast(bf16lo_to_f32(gr)), gelu_fast(bf16hi_to_f32(gr)));
+          float g0, g1;
+          gelu_fast2(bf16lo_to_f32(gr), bf16hi_to_f32(gr), g0, g1);
+          const uint32_t ar = pack_bf16x2(g0, g1);
           v[i + k] = bf16lo_to_f32(vr) * bf16lo_to_f32(ar);
           v[i + k + 1] = bf16hi_to_f32(vr) * bf16hi_to_f32(ar);
         }
@@ -171,8 +173,7 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {  // fc1's output is a bf16 tensor: round (paired convert), then GELU
           const uint32_t r = pack_bf16x2(v[i], v[i + 1]);
-          v[i] = gelu_fast(bf16lo_to_f32(r));
-          v[i + 1] = gelu_fast(bf16hi_to_f32(r));
+          gelu_fast2(bf16lo_to_f32(r), bf16hi_to_f32(r), v[i], v[i + 1]);
         }
       } else if (act == VDA_ACT_RELU) {
 #pragma unroll
