@@ -141,6 +141,19 @@ int vda_groupnorm_tokens(const void* x, int32_t x_dtype, void* y, int32_t y_dtyp
                          float eps, int32_t frames, int32_t hw, int32_t C, int32_t groups, double* stats,
                          vda_stream_t stream);
 
+/* Allocation-free variant of vda_groupnorm_tokens.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  Same kernels and results as vda_groupnorm_tokens; the statistics scratch
+ * lives in a file-scope static __device__ array of the library (1.06 MiB, held by every GPU that loads the library until
+ * the process exits) whose device address is resolved once per device with cudaGetSymbolAddress.  Limit:
+ * frames * groups <= vda_groupnorm_noalloc_max_frames_x_groups() (2048, e.g. 64 frames x 32 groups); larger calls
+ * return -1 with a message in vda_last_error().  The call performs no cudaMalloc / cudaFree and no other allocating
+ * call.  All calls on a device share the one array (it keeps the last call's contents; nothing in it has to start at
+ * zero): calls that overlap on the GPU -- different streams -- race, so serialise them on one stream. */
+int vda_groupnorm_tokens_noalloc(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, const float* w, const float* b,
+                                 float eps, int32_t frames, int32_t hw, int32_t C, int32_t groups, vda_stream_t stream);
+int32_t vda_groupnorm_noalloc_max_frames_x_groups(void);
+
 /* Encoder self-attention (dinov2_layers/attention.py:49-59): qkv[frames*ntok, 3*heads*64] -> o[frames*ntok, heads*64];
  * softmax(0.125 * q k^T) v per (frame, head).  head_dim is 64 for every DINOv2 size. */
 int vda_attention(const void* qkv, void* o, int32_t dtype, int32_t frames, int32_t ntok, int32_t heads,

@@ -294,3 +294,51 @@ extern "C" int vda_groupnorm_tokens(const void* x, int32_t x_dtype, void* y, int
   VDA_CUDA_LAUNCH_CHECK("groupnorm kernels");
   return 0;
 }
+
+// ---------------------------------------------------------------- allocation-free GroupNorm entry point
+// Same kernels as vda_groupnorm_tokens, with the statistics scratch in a file-scope device array instead of a caller
+// buffer, for callers that cannot allocate (CUDA graph capture, serving loops).  The array is part of the module image:
+// every GPU that loads the library holds VDA_GN_STATIC_MAX_FG * 2 * (GN_MAX_BLOCKS + 2) doubles (1.06 MiB) until exit.
+// In host code `g_gn_static_stats` is only a handle for the symbol, never a device address: the address is looked up
+// once per device with cudaGetSymbolAddress while that device is current.  All calls on one device share the array (it
+// keeps the previous call's contents; every slot a call reads is written by that call first, so nothing needs zeroing),
+// hence two calls that overlap on the GPU (different streams) race.
+constexpr int VDA_GN_STATIC_MAX_FG = 2048;  // frames * groups, e.g. 64 frames x 32 groups
+static __device__ __align__(256) double g_gn_static_stats[(size_t)VDA_GN_STATIC_MAX_FG * 2 * (GN_MAX_BLOCKS + 2)];
+
+static int gn_static_scratch(double** out) {
+  constexpr int MAX_DEV = 64;
+  static double* ptrs[MAX_DEV] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+    vda_set_error("vda_groupnorm_tokens_noalloc: cudaGetDevice failed or device %d out of range: %s", dev,
+                  cudaGetErrorString(e));
+    return e != cudaSuccess ? (int)e : -1;
+  }
+  double* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+  if (!p) {  // first call on this device (it is the current one); a concurrent first call resolves the same address
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gn_static_stats);
+    if (e != cudaSuccess || !p) {
+      vda_set_error("vda_groupnorm_tokens_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : -1;
+    }
+    __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return 0;
+}
+
+extern "C" int vda_groupnorm_tokens_noalloc(const void* x, int32_t x_dtype, void* y, int32_t y_dtype, const float* w,
+                                            const float* b, float eps, int32_t frames, int32_t hw, int32_t C,
+                                            int32_t groups, vda_stream_t stream) {
+  VDA_CHECK_ARG(frames > 0 && groups > 0 && (long long)frames * groups <= VDA_GN_STATIC_MAX_FG,
+                "vda_groupnorm_tokens_noalloc: frames * groups = %lld exceeds the static scratch (max %d); use "
+                "vda_groupnorm_tokens with a caller buffer", (long long)frames * groups, VDA_GN_STATIC_MAX_FG);
+  double* stats = nullptr;
+  const int rc = gn_static_scratch(&stats);
+  if (rc != 0) return rc;
+  return vda_groupnorm_tokens(x, x_dtype, y, y_dtype, w, b, eps, frames, hw, C, groups, stats, stream);
+}
+
+extern "C" int32_t vda_groupnorm_noalloc_max_frames_x_groups(void) { return VDA_GN_STATIC_MAX_FG; }
