@@ -197,6 +197,13 @@ int vda_output_head_f16(const void* x, const void* w_f16, const float* bias, con
 int vda_im2col_patch(const float* x, void* A, int32_t a_dtype, int32_t frames, int32_t H, int32_t W, int32_t kpad,
                      vda_stream_t stream);
 
+/* The same im2col with one pointer per frame: frame f is the planar [3, H, W] f32 image at frame_ptrs[f] (8-byte aligned).
+ * frame_ptrs is a DEVICE array of `frames` device pointers, read when the kernel runs -- the sliding-window driver rewrites
+ * it per window, so a window's 32 inputs (video_depth.py:358-364: new frames + the previous window's key frames) are
+ * gathered from the once-pre-processed frame pool by the patch-embed itself, also under a replayed CUDA graph. */
+int vda_im2col_patch_frames(const float* const* frame_ptrs, void* A, int32_t a_dtype, int32_t frames, int32_t H, int32_t W,
+                            int32_t kpad, vda_stream_t stream);
+
 /* Class-token rows of the residual stream (dinov2.py:220-221): resid[f*ntok, :] = cls + pos[0, :]. */
 int vda_cls_rows(float* resid, const float* cls, const float* pos, int32_t frames, int32_t ntok, int32_t D,
                  vda_stream_t stream);
@@ -223,6 +230,14 @@ int vda_resize_depth(const void* in, int32_t dtype, float* out, int32_t n, int32
  * over two frames (video_depth.py:390-395): call once per frame pair with phase 1 then 2. */
 int vda_scale_shift(const float* pred, const float* target, int64_t count, double* scratch, float* st, int32_t phase,
                     vda_stream_t stream);
+
+/* The same fit (utils/util.py:40-62, video_depth.py:390-395) over one contiguous (pred, target) pair with a DETERMINISTIC
+ * reduction: fixed 4096-element chunks -> partial[chunk][4] (f64), then one block adds the partials in a fixed order and
+ * solves.  No atomics; the result does not depend on the grid or the SM count, so every rank of a window-sharded run
+ * computes bit-identical (scale, shift).  partial: vda_scale_shift_det_workspace_doubles(count) doubles, fully rewritten. */
+int64_t vda_scale_shift_det_workspace_doubles(int64_t count);
+int vda_scale_shift_det(const float* pred, const float* target, int64_t count, double* partial, float* st,
+                        vda_stream_t stream);
 
 /* out = max(in*st[0] + st[1], 0) over count elements (video_depth.py:399-412). */
 int vda_scale_clamp(const float* in, float* out, const float* st, int64_t count, vda_stream_t stream);
@@ -268,6 +283,24 @@ int vda_depth_vis(const float* depth, int64_t count, const float* minmax, const 
 /* 8-frame linear cross-fade (utils/util.py:65-74, video_depth.py:397-402):
  * inout[i] = inout[i]*(1-w_i) + max(post[i]*st[0]+st[1], 0)*w_i, w = i/(n-1). */
 int vda_blend(float* inout, const float* post, const float* st, int32_t n, int64_t frame_elems, vda_stream_t stream);
+
+/* Plain device-to-device copy of `bytes` bytes on `stream` (window 0's frames enter the output un-scaled and un-clamped,
+ * video_depth.py:382-387; the exchange buffers of the window-sharded driver). */
+int vda_copy_device(const void* src, void* dst, int64_t bytes, vda_stream_t stream);
+
+/* Page-lock (cudaHostRegisterPortable) / release a HOST address range: each rank of a window-sharded run registers its
+ * mapping of the node-wide shared result buffer, so that its device->host copies of the final frames (video_depth.py:372
+ * in the reference: one blocking copy per frame) are asynchronous DMA over its own PCIe link.  On failure the error is
+ * returned (text in vda_last_error) and cleared from the CUDA runtime's last-error slot. */
+int vda_host_register(void* host_ptr, int64_t bytes);
+int vda_host_unregister(void* host_ptr);
+
+/* The same cross-fade from two RAW tails (window-sharded driver: the previous window's last n frames come un-aligned from
+ * the rank that owns it): out[i] = P*(1-w_i) + Q*w_i with P = max(pre[i]*st_pre[0]+st_pre[1], 0) (P = pre[i] when st_pre
+ * is NULL: window 0 is never scaled or clamped, video_depth.py:382-387) and Q = max(post[i]*st_post[0]+st_post[1], 0).
+ * Bit-identical to vda_scale_clamp into a buffer followed by vda_blend on it. */
+int vda_blend_raw(const float* pre, const float* st_pre, const float* post, const float* st_post, float* out, int32_t n,
+                  int64_t frame_elems, vda_stream_t stream);
 
 #ifdef __cplusplus
 }

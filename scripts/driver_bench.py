@@ -41,8 +41,8 @@ def main():
     from video_depth_anything_b200.driver import (WindowedDepthDriver, effective_input_size, network_size, window_index_map)
     model = build_model(a.encoder, dev)
     frames = synth(a.frames, a.h, a.w)
-    drv = WindowedDepthDriver(model, device=dev, fp32=False)
-    drv.run(frames[:40], a.input_size)  # warm-up: weights packed, plan built
+    drv = WindowedDepthDriver(model, device=dev, fp32=False, group=dist.group.WORLD if dist is not None else None)
+    drv.run(frames[:44 * world], a.input_size)  # warm-up: weights packed, plan built
     torch.cuda.synchronize()
     best = None
     for _ in range(a.repeat):

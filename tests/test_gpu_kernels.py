@@ -336,6 +336,81 @@ def test_driver_kernels():
     assert np.abs(pre.cpu().numpy() - refb).max() < 1e-6
 
 
+def test_preprocess_720p_to_518x924():
+    """BASELINE.json config 4's geometry: 720x1280 frames -> cv2.INTER_CUBIC to 518x924 -> normalise
+    (util/transform.py:109-158) against the oracle's cv2 path, and on a ratio > 1.78 frame (374x1242 -> 280x924)."""
+    from oracle import driver as odrv
+    from oracle.inputs import synthetic_video
+    L, lib = _lib()
+    st = L.stream_ptr()
+    for (fh, fw, want) in ((720, 1280, (518, 924)), (374, 1242, (280, 924))):
+        frames = synthetic_video(2, fh, fw, 3)
+        e = odrv.effective_input_size(fh, fw, 518)
+        nh, nw = odrv.network_size(fh, fw, e)
+        assert (nh, nw) == want
+        ref = np.stack([odrv.preprocess_frame(f, e) for f in frames])
+        fd = torch.from_numpy(frames).to(dev)
+        out = torch.zeros(2, 3, nh, nw, device=dev)
+        L.check(lib.vda_preprocess_u8(fd.data_ptr(), out.data_ptr(), 2, fh, fw, nh, nw, st), "pre")
+        s = stats(f"preprocess_{fh}x{fw}", out.cpu(), torch.from_numpy(ref))
+        # fp32 sums of four signed taps in another order than cv2's SIMD code: 4.0e-5 observed at the worst of 1.4 M values
+        # in [-2.2, 2.7] (1.5e-5 of the range, mean 2e-6); the small cases of test_driver_kernels hold 2e-5
+        assert s["max_abs"] < 1e-4 and s["mean_abs"] < 5e-6
+
+
+def test_sharded_stitch_kernels():
+    """vda_scale_shift_det (deterministic, grid-independent), vda_blend_raw (bit-identical to vda_scale_clamp + vda_blend),
+    vda_copy_device, vda_im2col_patch_frames (bit-identical to vda_im2col_patch on gathered frames)."""
+    from oracle import driver as odrv
+    L, lib = _lib()
+    st = L.stream_ptr()
+    g = torch.Generator(device="cpu").manual_seed(5)
+    for count in (2 * 33 * 47, 4096, 4097, 2 * 720 * 1280):
+        p = (torch.rand(count, generator=g) * 20).to(dev)
+        t = p * 1.7 + 0.3 + torch.randn(count, generator=g).to(dev) * 0.01
+        nws = int(lib.vda_scale_shift_det_workspace_doubles(count))
+        assert nws == ((count + 4095) // 4096) * 4
+        outs = []
+        for rep in range(3):   # poisoned scratch, repeated: bit-identical every time
+            ws = torch.full((nws,), float("nan") if rep else 7.0, dtype=torch.float64, device=dev)
+            stt = torch.zeros(2, device=dev)
+            L.check(lib.vda_scale_shift_det(p.data_ptr(), t.data_ptr(), count, ws.data_ptr(), stt.data_ptr(), st), "ls_det")
+            outs.append(stt.cpu().numpy().copy())
+        assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+        s64, t64 = np.polyfit(p.double().cpu().numpy(), t.double().cpu().numpy(), 1)
+        assert abs(outs[0][0] - s64) < 2e-6 and abs(outs[0][1] - t64) < 2e-5, (outs[0], s64, t64)
+        s_ref, t_ref = odrv.compute_scale_and_shift(p.cpu().numpy(), t.cpu().numpy(), np.ones(count) == 1)
+        assert abs(outs[0][0] - s_ref) < 1e-3 and abs(outs[0][1] - t_ref) < 1e-2   # the reference's fp32 numpy sums are the noisy side
+    fe = 45 * 63   # not a multiple of 4: unaligned frames
+    pre_raw = (torch.randn(8, fe, generator=g) * 3).to(dev)
+    post_raw = (torch.randn(8, fe, generator=g) * 3).to(dev)
+    st0 = torch.tensor([1.3, -0.2], device=dev)
+    st1 = torch.tensor([0.7, 0.4], device=dev)
+    for with_pre in (True, False):
+        a = torch.empty_like(pre_raw)
+        if with_pre:
+            L.check(lib.vda_scale_clamp(pre_raw.data_ptr(), a.data_ptr(), st0.data_ptr(), pre_raw.numel(), st), "sc")
+        else:
+            L.check(lib.vda_copy_device(pre_raw.data_ptr(), a.data_ptr(), pre_raw.numel() * 4, st), "copy")
+            assert torch.equal(a, pre_raw)
+        L.check(lib.vda_blend(a.data_ptr(), post_raw.data_ptr(), st1.data_ptr(), 8, fe, st), "blend")
+        b = torch.empty_like(pre_raw)
+        L.check(lib.vda_blend_raw(pre_raw.data_ptr(), st0.data_ptr() if with_pre else None, post_raw.data_ptr(), st1.data_ptr(),
+                                  b.data_ptr(), 8, fe, st), "blend_raw")
+        assert torch.equal(a, b)
+    for dt, H, W in ((torch.bfloat16, 28, 42), (torch.float32, 28, 42), (torch.bfloat16, 14, 14)):
+        pool = torch.randn(7, 3, H, W, generator=g).to(dev)
+        sel = [6, 0, 3, 3, 1]
+        ptrs = torch.tensor([pool[i].data_ptr() for i in sel], dtype=torch.int64).to(dev)
+        rows = len(sel) * (H // 14) * (W // 14)
+        A0 = torch.zeros(rows, 640, dtype=dt, device=dev)
+        A1 = torch.ones(rows, 640, dtype=dt, device=dev)
+        xs = pool[sel].contiguous()
+        L.check(lib.vda_im2col_patch(xs.data_ptr(), A0.data_ptr(), L.dt(A0), len(sel), H, W, 640, st), "im2col")
+        L.check(lib.vda_im2col_patch_frames(ptrs.data_ptr(), A1.data_ptr(), L.dt(A1), len(sel), H, W, 640, st), "im2col_frames")
+        assert torch.equal(A0, A1) and A0.float().abs().max().item() > 1
+
+
 @pytest.mark.parametrize("mode", ["f32", "bf16"])
 def test_rope_qk(mode):
     """vda_rope_qk against `apply_rotary_emb` restated with torch complex arithmetic (motion_module/attention.py:419-429)."""

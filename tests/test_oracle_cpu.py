@@ -187,9 +187,9 @@ def test_product_host_geometry_matches_oracle():
     assert odrv.network_size(720, 1280, 518) == (518, 924)
     assert odrv.network_size(374, 1242, odrv.effective_input_size(374, 1242, 518)) == (280, 924)
     for nw, world in [(47, 8), (94, 8), (3, 8), (1, 2), (5, 2)]:
-        sh = pdrv.shard_windows(nw, world)
-        assert sum(c for _, c in sh) == nw and len(sh) == world
-        assert all(sh[i][0] + sh[i][1] == sh[i + 1][0] for i in range(world - 1) if sh[i + 1][1] > 0)
+        owned = [pdrv.rank_windows(nw, world, r) for r in range(world)]
+        assert sorted(k for o in owned for k in o) == list(range(nw))
+        assert max(len(o) for o in owned) - min(len(o) for o in owned) <= 1
 
 
 def test_scale_shift_known_answer():

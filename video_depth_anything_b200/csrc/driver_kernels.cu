@@ -242,6 +242,98 @@ __global__ void __launch_bounds__(256) blend_kernel(float* __restrict__ inout, c
   }
 }
 
+
+// Deterministic form of the least-squares sums (the window-sharded driver evaluates the (scale, shift) recurrence
+// redundantly on every rank and needs bit-identical results everywhere, and equal to a single-rank run): block c sums
+// elements [c*LS_CHUNK, (c+1)*LS_CHUNK) in a fixed order (per-thread strided sums, shuffle tree, warp order) into
+// partial[c][0..3]; one block then adds the partials in a fixed order (thread t takes c = t, t+256, ...; shuffle tree;
+// warp order) and solves.  No atomics, and no dependence on the grid size or the SM count.
+constexpr int LS_CHUNK = 4096;
+
+__global__ void __launch_bounds__(256) ls_partial_kernel(const float* __restrict__ pred, const float* __restrict__ tgt,
+                                                        long long count, double* __restrict__ partial) {
+  double s[4] = {0, 0, 0, 0};  // sum p*p, sum p, sum p*t, sum t
+  const long long base = (long long)blockIdx.x * LS_CHUNK;
+  const long long end = min(count, base + LS_CHUNK);
+  for (long long i = base + threadIdx.x; i < end; i += 256) {
+    const double p = pred[i], t = tgt[i];
+    s[0] += p * p; s[1] += p; s[2] += p * t; s[3] += t;
+  }
+  __shared__ double sh[4][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
+    if (lane == 0) sh[k][warp] = s[k];
+  }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    double t = 0;
+    for (int w = 0; w < 8; ++w) t += sh[threadIdx.x][w];
+    partial[(long long)blockIdx.x * 4 + threadIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256) ls_final_kernel(const double* __restrict__ partial, int chunks, long long count,
+                                                      float* __restrict__ st) {
+  double s[4] = {0, 0, 0, 0};
+  for (int c = threadIdx.x; c < chunks; c += 256) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s[k] += partial[(long long)c * 4 + k];
+  }
+  __shared__ double sh[4][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
+    if (lane == 0) sh[k][warp] = s[k];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t[4];
+    for (int k = 0; k < 4; ++k) {
+      t[k] = 0;
+      for (int w = 0; w < 8; ++w) t[k] += sh[k][w];
+    }
+    const double a00 = t[0], a01 = t[1], b0 = t[2], b1 = t[3], a11 = (double)count;
+    const double det = a00 * a11 - a01 * a01;
+    double x0 = 1.0, x1 = 0.0;
+    if (det != 0.0) {
+      x0 = (a11 * b0 - a01 * b1) / det;
+      x1 = (-a01 * b0 + a00 * b1) / det;
+    }
+    st[0] = (float)x0;
+    st[1] = (float)x1;
+  }
+}
+
+// Cross-fade of two RAW tails (window-sharded driver): the previous window's last frames arrive un-aligned from their
+// owner, so both sides are aligned here.  Same fp32 operations, in the same order, as scale_clamp_kernel followed by
+// blend_kernel (bit-identical to the single-buffer form).  st_pre == NULL: `pre` is used as it is (window 0's frames are
+// never scaled or clamped, video_depth.py:382-387).
+__global__ void __launch_bounds__(256) blend_raw_kernel(const float* __restrict__ pre, const float* __restrict__ st_pre,
+                                                       const float* __restrict__ post, const float* __restrict__ st_post,
+                                                       float* __restrict__ out, int n, long long frame_elems) {
+  const float s1 = st_post[0], t1 = st_post[1];
+  const bool has0 = st_pre != nullptr;
+  const float s0 = has0 ? st_pre[0] : 1.f, t0 = has0 ? st_pre[1] : 0.f;
+  const int f = blockIdx.y;
+  const double step = 1.0 / (double)(n - 1);
+  const double wd = (f == 0) ? 0.0 : (f == n - 1 ? 1.0 : f * step);
+  const float w1 = (float)wd, w0 = (float)(1.0 - wd);
+  const float* a = pre + (long long)f * frame_elems;
+  const float* b = post + (long long)f * frame_elems;
+  float* o = out + (long long)f * frame_elems;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < frame_elems;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float av = has0 ? fmaxf(__fadd_rn(__fmul_rn(a[i], s0), t0), 0.f) : a[i];
+    const float pv = fmaxf(__fadd_rn(__fmul_rn(b[i], s1), t1), 0.f);
+    o[i] = __fadd_rn(__fmul_rn(av, w0), __fmul_rn(pv, w1));
+  }
+}
+
 }  // namespace
 
 extern "C" int vda_preprocess_u8(const uint8_t* frames, float* out, int32_t n, int32_t fh, int32_t fw, int32_t oh,
@@ -369,5 +461,66 @@ extern "C" int vda_blend(float* inout, const float* post, const float* st, int32
   if (bx < 1) bx = 1;
   blend_kernel<<<dim3(bx, n), 256, 0, s>>>(inout, post, st, n, frame_elems);
   VDA_CUDA_LAUNCH_CHECK("blend_kernel");
+  return 0;
+}
+
+extern "C" int64_t vda_scale_shift_det_workspace_doubles(int64_t count) {
+  return count <= 0 ? 4 : ((count + LS_CHUNK - 1) / LS_CHUNK) * 4;
+}
+
+extern "C" int vda_scale_shift_det(const float* pred, const float* target, int64_t count, double* partial, float* st,
+                                   vda_stream_t stream) {
+  VDA_CHECK_ARG(count > 0 && count <= (int64_t)LS_CHUNK * 0x7fffffff, "vda_scale_shift_det: bad count %lld", (long long)count);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const long long chunks = (count + LS_CHUNK - 1) / LS_CHUNK;
+  ls_partial_kernel<<<(unsigned)chunks, 256, 0, s>>>(pred, target, count, partial);
+  ls_final_kernel<<<1, 256, 0, s>>>(partial, (int)chunks, count, st);
+  VDA_CUDA_LAUNCH_CHECK("scale_shift_det kernels");
+  return 0;
+}
+
+extern "C" int vda_blend_raw(const float* pre, const float* st_pre, const float* post, const float* st_post, float* out,
+                             int32_t n, int64_t frame_elems, vda_stream_t stream) {
+  VDA_CHECK_ARG(n >= 2, "vda_blend_raw: n must be >= 2");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  int bx = (int)((frame_elems + 256 * 4 - 1) / (256 * 4));
+  if (bx > 2 * vda_sm_count()) bx = 2 * vda_sm_count();
+  if (bx < 1) bx = 1;
+  blend_raw_kernel<<<dim3(bx, n), 256, 0, s>>>(pre, st_pre, post, st_post, out, n, frame_elems);
+  VDA_CUDA_LAUNCH_CHECK("blend_raw_kernel");
+  return 0;
+}
+
+extern "C" int vda_copy_device(const void* src, void* dst, int64_t bytes, vda_stream_t stream) {
+  if (bytes <= 0) return 0;
+  cudaError_t e = cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, reinterpret_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) {
+    vda_set_error("vda_copy_device: cudaMemcpyAsync failed: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
+}
+
+// Page-lock / release a HOST range (the node-wide result buffer of the window-sharded driver is shared memory mapped by
+// every rank: each process registers its mapping so that its device->host copies are asynchronous DMA).  A failed
+// registration is reported and cleared from the runtime's sticky last-error slot, so the caller can fall back to staged
+// copies without poisoning the next CUDA call.
+extern "C" int vda_host_register(void* host_ptr, int64_t bytes) {
+  cudaError_t e = cudaHostRegister(host_ptr, (size_t)bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) {
+    vda_set_error("vda_host_register(%p, %lld): %s", host_ptr, (long long)bytes, cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return (int)e;
+  }
+  return 0;
+}
+
+extern "C" int vda_host_unregister(void* host_ptr) {
+  cudaError_t e = cudaHostUnregister(host_ptr);
+  if (e != cudaSuccess) {
+    vda_set_error("vda_host_unregister(%p): %s", host_ptr, cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return (int)e;
+  }
   return 0;
 }

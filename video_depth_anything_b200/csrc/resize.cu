@@ -77,8 +77,8 @@ __global__ void __launch_bounds__(256) bilinear_kernel(const T* __restrict__ in,
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) im2col_patch_kernel(const float* __restrict__ x, T* __restrict__ A, int H, int W,
-                                                          int kpad, long long total) {
+__global__ void __launch_bounds__(256) im2col_patch_kernel(const float* __restrict__ x, const float* const* __restrict__ fptr,
+                                                          T* __restrict__ A, int H, int W, int kpad, long long total) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int k = (int)(idx % kpad);
@@ -90,7 +90,8 @@ __global__ void __launch_bounds__(256) im2col_patch_kernel(const float* __restri
   float v = 0.f;
   if (k < 588) {
     const int c = k / 196, r = k % 196, i = r / 14, j = r % 14;
-    v = x[(((long long)f * 3 + c) * H + py * 14 + i) * W + px * 14 + j];
+    const float* img = fptr ? fptr[f] : x + (long long)f * 3 * H * W;  // per-frame pointers: the driver's window gather
+    v = img[((long long)c * H + py * 14 + i) * W + px * 14 + j];
   }
   A[idx] = from_f32<T>(v);
 }
@@ -98,8 +99,8 @@ __global__ void __launch_bounds__(256) im2col_patch_kernel(const float* __restri
 // bf16 fast path: one thread per 14-pixel patch row (56 contiguous input bytes as seven float2, 28 output bytes as seven
 // bf16 pairs), 42 such rows per patch plus one thread for the zero tail [588, kpad); consecutive threads write
 // consecutive pieces of the same A row.  The element-per-thread form above moved 2 bytes per store instruction.
-__global__ void __launch_bounds__(256) im2col_patch_rows_kernel(const float* __restrict__ x, bf16* __restrict__ A, int H, int W,
-                                                               int kpad, long long tasks) {
+__global__ void __launch_bounds__(256) im2col_patch_rows_kernel(const float* __restrict__ x, const float* const* __restrict__ fptr,
+                                                               bf16* __restrict__ A, int H, int W, int kpad, long long tasks) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= tasks) return;
   const int r = (int)(idx % 43);   // 0..41: (channel, patch row); 42: the padding tail
@@ -115,7 +116,8 @@ __global__ void __launch_bounds__(256) im2col_patch_rows_kernel(const float* __r
   const int py = (int)((m / pw) % ph);
   const int f = (int)(m / ((long long)pw * ph));
   const int c = r / 14, i = r - c * 14;
-  const float2* in = reinterpret_cast<const float2*>(x + (((long long)f * 3 + c) * H + py * 14 + i) * W + px * 14);
+  const float* img = fptr ? fptr[f] : x + (long long)f * 3 * H * W;
+  const float2* in = reinterpret_cast<const float2*>(img + ((long long)c * H + py * 14 + i) * W + px * 14);
   uint32_t* o = reinterpret_cast<uint32_t*>(out + r * 14);
   float2 v[7];
 #pragma unroll
@@ -194,20 +196,34 @@ extern "C" int vda_bilinear(const void* in, int32_t in_dtype, void* out, int32_t
   return 0;
 }
 
+static int im2col_patch_launch(const float* x, const float* const* fptr, bool aligned8, void* A, int32_t a_dtype, int32_t frames,
+                               int32_t H, int32_t W, int32_t kpad, cudaStream_t st) {
+  const long long total = (long long)frames * (H / 14) * (W / 14) * kpad;
+  const unsigned grid = (unsigned)((total + 255) / 256);
+  if (a_dtype == VDA_BF16 && W % 2 == 0 && kpad % 2 == 0 && kpad >= 588 && aligned8 && ((uintptr_t)A % 4) == 0) {
+    const long long tasks = (long long)frames * (H / 14) * (W / 14) * 43;
+    im2col_patch_rows_kernel<<<(unsigned)((tasks + 255) / 256), 256, 0, st>>>(x, fptr, (bf16*)A, H, W, kpad, tasks);
+  } else if (a_dtype == VDA_BF16) im2col_patch_kernel<bf16><<<grid, 256, 0, st>>>(x, fptr, (bf16*)A, H, W, kpad, total);
+  else im2col_patch_kernel<float><<<grid, 256, 0, st>>>(x, fptr, (float*)A, H, W, kpad, total);
+  VDA_CUDA_LAUNCH_CHECK("im2col_patch_kernel");
+  return 0;
+}
+
 extern "C" int vda_im2col_patch(const float* x, void* A, int32_t a_dtype, int32_t frames, int32_t H, int32_t W,
                                 int32_t kpad, vda_stream_t stream) {
   VDA_CHECK_ARG(H % 14 == 0 && W % 14 == 0, "vda_im2col_patch: H, W must be multiples of 14 (patch_embed.py:73-74)");
   VDA_CHECK_ARG(kpad >= 588, "vda_im2col_patch: kpad < 588");
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const long long total = (long long)frames * (H / 14) * (W / 14) * kpad;
-  const unsigned grid = (unsigned)((total + 255) / 256);
-  if (a_dtype == VDA_BF16 && W % 2 == 0 && kpad % 2 == 0 && kpad >= 588 && ((uintptr_t)x % 8) == 0 && ((uintptr_t)A % 4) == 0) {
-    const long long tasks = (long long)frames * (H / 14) * (W / 14) * 43;
-    im2col_patch_rows_kernel<<<(unsigned)((tasks + 255) / 256), 256, 0, st>>>(x, (bf16*)A, H, W, kpad, tasks);
-  } else if (a_dtype == VDA_BF16) im2col_patch_kernel<bf16><<<grid, 256, 0, st>>>(x, (bf16*)A, H, W, kpad, total);
-  else im2col_patch_kernel<float><<<grid, 256, 0, st>>>(x, (float*)A, H, W, kpad, total);
-  VDA_CUDA_LAUNCH_CHECK("im2col_patch_kernel");
-  return 0;
+  return im2col_patch_launch(x, nullptr, ((uintptr_t)x % 8) == 0, A, a_dtype, frames, H, W, kpad,
+                             reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int vda_im2col_patch_frames(const float* const* frame_ptrs, void* A, int32_t a_dtype, int32_t frames, int32_t H,
+                                       int32_t W, int32_t kpad, vda_stream_t stream) {
+  VDA_CHECK_ARG(H % 14 == 0 && W % 14 == 0, "vda_im2col_patch_frames: H, W must be multiples of 14 (patch_embed.py:73-74)");
+  VDA_CHECK_ARG(kpad >= 588 && frame_ptrs != nullptr, "vda_im2col_patch_frames: kpad < 588 or null pointer table");
+  // the pointer table lives on the device (it changes per window under a replayed CUDA graph), so alignment of the frames
+  // is the caller's contract: 8-byte aligned planar [3, H, W] fp32 images
+  return im2col_patch_launch(nullptr, frame_ptrs, true, A, a_dtype, frames, H, W, kpad, reinterpret_cast<cudaStream_t>(stream));
 }
 
 extern "C" int vda_cls_rows(float* resid, const float* cls, const float* pos, int32_t frames, int32_t ntok, int32_t D,

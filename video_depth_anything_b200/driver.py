@@ -1,20 +1,28 @@
 """The sliding-window driver: `VideoDepthAnything.infer_video_depth` (reference video_depth.py:329-417).
 
-What the reference does on the host with cv2 / numpy (pre-processing 32x per window, per-frame D2H, numpy
-least squares and blending) runs here on the device, asynchronously on one stream: every source frame is
-pre-processed once, windows gather their 32 inputs by index (the window contents are pure index arithmetic,
-video_depth.py:350-364), and the sequential scale/shift recurrence keeps (scale, shift) in device memory, so there
-is exactly one device->host copy: the final [N, H, W] stack.
+What the reference does on the host with cv2 / numpy (pre-processing 32x per window, per-frame D2H, numpy least squares
+and blending) runs here on the device, as a pipeline over three streams: every source frame is uploaded and
+pre-processed once (upload stream), windows gather their 32 inputs by pointer (the window contents are pure index
+arithmetic, video_depth.py:350-364) and run the network (main stream), and each finished window is aligned, cross-faded
+and copied to the host while the next one computes (stitch stream).
 
-Window-level data parallelism: with `torch.distributed` initialised, windows are dealt to
-ranks in contiguous blocks; every rank runs its forwards, rank 0 gathers the raw per-window depth maps (NCCL) and
-runs the cheap sequential stitching pass.  No collective runs inside a forward.
+Window-level data parallelism, opt-in through a process group: window k belongs to rank
+k % world, so every `world` consecutive windows form a ROUND that the ranks compute at the same time.  No collective runs
+inside a forward.  After its forward a rank shares 11 raw frames of its window with the others (one all-gather per round
+over NCCL / NVLink): slots 0, 1 (the two frames of the scale/shift fit), slot 12 (the next window's alignment target) and
+slots 24..31 (the tail its successor cross-fades with).  Every rank then replays the scalar (scale, shift) recurrence of
+the round (video_depth.py:393-395,409-413) with a deterministic reduction -- bit-identical on all ranks and to a
+one-rank run -- finalises the 22 frames its own window contributes, and copies them over ITS OWN PCIe link into a host
+buffer shared by the ranks of the node.  The result is bit-identical to a single-rank run.
 """
 from __future__ import annotations
 
+import mmap
+import os
 import queue
 import threading
 import time
+import warnings
 
 import numpy as np
 import torch
@@ -27,6 +35,9 @@ KEYFRAMES = [0, 12, 24, 25, 26, 27, 28, 29, 30, 31]
 INTERP_LEN = 8
 FRAME_STEP = INFER_LEN - OVERLAP
 ALIGN_LEN = OVERLAP - INTERP_LEN
+# what a window shares with the other ranks: the fit frames (0, 1), the next alignment target (12), the cross-fade tail
+XCHG_SLOTS = list(range(ALIGN_LEN)) + [KEYFRAMES[1]] + list(range(INFER_LEN - INTERP_LEN, INFER_LEN))
+XCHG_FIT, XCHG_REF, XCHG_TAIL = slice(0, ALIGN_LEN), ALIGN_LEN, slice(ALIGN_LEN + 1, ALIGN_LEN + 1 + INTERP_LEN)
 
 
 def effective_input_size(frame_h: int, frame_w: int, input_size: int) -> int:
@@ -66,18 +77,152 @@ def window_index_map(n_frames: int) -> np.ndarray:
     return idx
 
 
-def shard_windows(n_windows: int, world: int):
-    """Contiguous blocks of windows per rank; [(first, count)] * world."""
-    per = (n_windows + world - 1) // world
-    out = []
-    for r in range(world):
-        lo = min(r * per, n_windows)
-        out.append((lo, max(0, min(per, n_windows - lo))))
-    return out
+def rank_windows(n_windows: int, world: int, rank: int):
+    """Windows of `rank`: k = rank, rank + world, ... (round j holds windows j*world .. j*world + world - 1)."""
+    return list(range(rank, n_windows, world))
+
+
+def final_range(k: int, n_windows: int):
+    """Output frames [lo, hi) that window k finalises (video_depth.py:379-415): window 0 its first 24 frames, window k >= 1
+    the 8 frames it cross-fades with its predecessor's tail (22k+2 ..) and its next 14; the last window also its tail."""
+    lo = 0 if k == 0 else FRAME_STEP * k + ALIGN_LEN
+    hi = FRAME_STEP * k + INFER_LEN - INTERP_LEN
+    if k == n_windows - 1:
+        hi += INTERP_LEN
+    return lo, hi
+
+
+def upload_runs(idx_rows):
+    """For a rank's windows in processing order: the source frames each one has to upload (those not seen before), as runs
+    of consecutive ids, and the pool row of every frame.  Returns (rowmap {id: row}, [[(first_id, count, first_row)]])."""
+    rowmap, per_window = {}, []
+    for row in idx_rows:
+        new = sorted(set(int(i) for i in row) - set(rowmap))
+        runs = []
+        for i in new:
+            rowmap[i] = len(rowmap)
+            if runs and runs[-1][0] + runs[-1][1] == i:
+                runs[-1][1] += 1
+            else:
+                runs.append([i, 1, rowmap[i]])
+        per_window.append([tuple(r) for r in runs])
+    return rowmap, per_window
+
+
+class WindowStitcher:
+    """One round of the sharded stitching pass: exchange, (scale, shift) recurrence, finalisation of this rank's window.
+
+    Pure orchestration: the arithmetic goes through `ops` (the C-ABI kernels in the product, `CudaStitchOps`; the CPU
+    tests drive the same orchestration with an oracle-backed ops object over gloo), buffers through `alloc`, the exchange
+    through `all_gather(dst[world, 11, ...], src[11, ...])` (None for a single rank).
+    """
+
+    def __init__(self, ops, n_frames, world, rank, frame_shape, alloc, all_gather=None):
+        self.ops, self.n, self.world, self.rank = ops, int(n_frames), int(world), int(rank)
+        self.n_win = (self.n + FRAME_STEP - 1) // FRAME_STEP
+        self.rounds = (self.n_win + self.world - 1) // self.world
+        self.all_gather = all_gather if self.world > 1 else None
+        nx = len(XCHG_SLOTS)
+        fs = tuple(frame_shape)
+        self.xchg = [alloc((self.world, nx) + fs), alloc((self.world, nx) + fs)]   # round j -> buffer j & 1
+        self.send = [alloc((nx,) + fs), alloc((nx,) + fs)]
+        self.ref = alloc((ALIGN_LEN,) + fs)      # [depth of video frame 0, previous window's aligned slot 12]
+        self.st = alloc((self.n_win, 2))         # (scale, shift) of every window; row 0 is never read (identity)
+        self.exchange_bytes_per_round = 0 if self.all_gather is None else nx * int(np.prod(fs)) * 4 * (self.world - 1)
+
+    def send_buffer(self, j):
+        """Where the owner of this rank's window of round j puts the window's raw XCHG_SLOTS frames before `round(j)`."""
+        return self.send[j & 1]
+
+    def exchange(self, j):
+        if self.all_gather is not None:
+            self.all_gather(self.xchg[j & 1], self.send[j & 1])
+        else:   # a single rank: the send buffer is free again for round j + 2 while round j + 1 still reads this round's tail
+            self.ops.align(self.send[j & 1], None, self.xchg[j & 1][0])
+
+    def round(self, j, raw, out):
+        """raw: [32, ...] raw depth of this rank's window of round j (None if it has none).  Writes the window's final
+        frames to out[0:count] and returns (first_frame, count) with count clipped to the video length, or None."""
+        ops, X = self.ops, self.xchg[j & 1]
+        first = j * self.world
+        for r in range(self.world):   # the scalar recurrence, replayed identically on every rank
+            k = first + r
+            if k >= self.n_win:
+                break
+            if k == 0:
+                ops.align(X[0][0:1], None, self.ref[0:1])
+                ops.align(X[0][XCHG_REF:XCHG_REF + 1], None, self.ref[1:2])
+            else:
+                ops.fit(X[r][XCHG_FIT], self.ref, self.st[k])
+                ops.align(X[r][XCHG_REF:XCHG_REF + 1], self.st[k], self.ref[1:2])
+        k = first + self.rank
+        if k >= self.n_win or raw is None:
+            return None
+        lo, _ = final_range(k, self.n_win)
+        if k == 0:
+            cnt = INFER_LEN - INTERP_LEN
+            ops.align(raw[0:cnt], None, out[0:cnt])   # window 0 is used as it is (video_depth.py:382-387)
+        else:
+            prev = X[self.rank - 1][XCHG_TAIL] if self.rank > 0 else self.xchg[(j & 1) ^ 1][self.world - 1][XCHG_TAIL]
+            st_prev = self.st[k - 1] if k - 1 > 0 else None
+            ops.blend(prev, st_prev, raw[ALIGN_LEN:OVERLAP], self.st[k], out[0:INTERP_LEN])
+            ops.align(raw[OVERLAP:INFER_LEN - INTERP_LEN], self.st[k], out[INTERP_LEN:FRAME_STEP])
+            cnt = FRAME_STEP
+        if k == self.n_win - 1:
+            ops.align(raw[INFER_LEN - INTERP_LEN:INFER_LEN], self.st[k] if k > 0 else None, out[cnt:cnt + INTERP_LEN])
+            cnt += INTERP_LEN
+        return lo, max(0, min(lo + cnt, self.n) - lo)
+
+
+class CudaStitchOps:
+    """The stitching arithmetic on the device, through the C ABI, on the current stream."""
+
+    def __init__(self, lib, frame_elems, device):
+        self.lib, self.fe = lib, int(frame_elems)
+        n = int(lib.vda_scale_shift_det_workspace_doubles(ALIGN_LEN * self.fe))
+        self.partial = torch.empty((n,), dtype=torch.float64, device=device)
+
+    def fit(self, pred, ref, st):
+        L.check(self.lib.vda_scale_shift_det(pred.data_ptr(), ref.data_ptr(), pred.shape[0] * self.fe, self.partial.data_ptr(),
+                                             st.data_ptr(), L.stream_ptr()), "vda_scale_shift_det")
+
+    def align(self, src, st, dst):
+        count = src.shape[0] * self.fe
+        if st is None:
+            L.check(self.lib.vda_copy_device(src.data_ptr(), dst.data_ptr(), count * 4, L.stream_ptr()), "vda_copy_device")
+        else:
+            L.check(self.lib.vda_scale_clamp(src.data_ptr(), dst.data_ptr(), st.data_ptr(), count, L.stream_ptr()), "vda_scale_clamp")
+
+    def blend(self, pre, st_pre, post, st_post, dst):
+        L.check(self.lib.vda_blend_raw(pre.data_ptr(), L._ptr(st_pre), post.data_ptr(), st_post.data_ptr(), dst.data_ptr(),
+                                       pre.shape[0], self.fe, L.stream_ptr()), "vda_blend_raw")
+
+
+def open_shared_buffer(nbytes, group):
+    """A host buffer of `nbytes` mapped by every rank of `group` (one node): anonymous shared memory created by group rank 0
+    (memfd: not bounded by the size of the /dev/shm mount) and opened by the others through /proc.  Returns the mmap."""
+    dist = torch.distributed
+    rank = dist.get_rank(group)
+    src = dist.get_global_rank(group, 0) if group is not None else 0
+    fd = -1
+    name = [None]
+    if rank == 0:
+        fd = os.memfd_create("vda_b200_result")
+        os.ftruncate(fd, nbytes)
+        name = [f"/proc/{os.getpid()}/fd/{fd}"]
+    dist.broadcast_object_list(name, src=src, group=group)
+    if rank != 0:
+        fd = os.open(name[0], os.O_RDWR)
+    mm = mmap.mmap(fd, nbytes)
+    dist.barrier(group)   # everybody holds a mapping before the creator's descriptor goes away
+    os.close(fd)
+    return mm
 
 
 class WindowedDepthDriver:
-    def __init__(self, model, device="cuda", fp32=False, skip_tmp_block=False, upload_chunk=64, distributed=True, streaming=True):
+    def __init__(self, model, device="cuda", fp32=False, skip_tmp_block=False, upload_chunk=64, group=None):
+        """group: None = this process alone (the reference's behaviour, whatever process group may exist); a
+        torch.distributed process group (e.g. `torch.distributed.group.WORLD`) = shard the windows over its ranks."""
         self.model = model
         self.device = torch.device(device)
         if self.device.type == "cuda" and self.device.index is None:
@@ -86,230 +231,243 @@ class WindowedDepthDriver:
         self.fp32 = fp32
         self.skip_tmp_block = skip_tmp_block
         self.upload_chunk = upload_chunk
-        self.distributed = distributed  # False: ignore an initialised process group (single-rank reference runs)
-        self.streaming = streaming      # single rank: pipeline upload / forward / stitch / download window by window
+        self.group = group
         self.lib = L.load()
         self.last_scale_shift = None
         self.last_stage_s = None
+        self.last_frame_ranges = None
 
-    # ------------------------------------------------------------------ stages
-    def preprocess(self, frames, ids, nh, nw):
-        """Source frames `ids` (sorted unique) -> {id: row} and device tensor [len(ids), 3, nh, nw] fp32
-        (util/transform.py:109-158 + video_depth.py:361, once per source frame)."""
-        fh, fw = frames[0].shape[:2]
-        out = torch.empty((len(ids), 3, nh, nw), dtype=torch.float32, device=self.device)
-        st = L.stream_ptr()
-        for c0 in range(0, len(ids), self.upload_chunk):
-            chunk = ids[c0:c0 + self.upload_chunk]
-            host = np.ascontiguousarray(np.stack([np.asarray(frames[int(i)]) for i in chunk]))
-            if host.dtype != np.uint8:
-                raise TypeError("frames must be uint8 [N,H,W,3]")
-            dev = torch.from_numpy(host).to(self.device, non_blocking=True)
-            L.check(self.lib.vda_preprocess_u8(dev.data_ptr(), out[c0].data_ptr(), len(chunk), fh, fw, nh, nw, st),
-                    "vda_preprocess_u8")
-            del dev
-        return {int(i): r for r, i in enumerate(ids)}, out
-
-    def forward_windows(self, pre, rowmap, idx_rows, nh, nw, fh, fw):
-        """Run the network on the given windows; returns raw depth [n_win*32, fh, fw] fp32 on device."""
-        bf16 = not self.fp32
-        plan = self.model.plan(1, INFER_LEN, nh, nw, self.device, bf16, self.skip_tmp_block)
-        raw = torch.empty((len(idx_rows) * INFER_LEN, fh, fw), dtype=torch.float32, device=self.device)
-        st = L.stream_ptr()
-        sel_all = torch.as_tensor([[rowmap[int(i)] for i in row] for row in idx_rows], dtype=torch.int64).to(self.device)
-        for k in range(len(idx_rows)):
-            torch.index_select(pre, 0, sel_all[k], out=plan.x_in)
-            plan.launch()
-            L.check(self.lib.vda_resize_depth(plan.depth.data_ptr(), L.F32, raw[k * INFER_LEN].data_ptr(), INFER_LEN,
-                                              nh, nw, fh, fw, st), "vda_resize_depth")
-        return raw
-
-    def stitch(self, raw, n_frames):
-        """Scale/shift alignment + overlap blend over all windows (video_depth.py:379-417), on device."""
-        n_win = raw.shape[0] // INFER_LEN
-        fh, fw = raw.shape[1:]
-        fe = fh * fw
-        total = INFER_LEN + FRAME_STEP * (n_win - 1)
-        out = torch.empty((total, fh, fw), dtype=torch.float32, device=self.device)
-        out[:INFER_LEN].copy_(raw[:INFER_LEN])
-        ref = torch.stack([raw[KEYFRAMES[0]], raw[KEYFRAMES[1]]]).contiguous()   # frame 0 of the video + slot 12
-        st_all = torch.zeros((n_win, 2), dtype=torch.float32, device=self.device)
-        st_all[0, 0] = 1.0
-        scratch = torch.zeros(5, dtype=torch.float64, device=self.device)
-        s = L.stream_ptr()
-        pos = INFER_LEN
-        for k in range(1, n_win):
-            cur = raw[k * INFER_LEN:(k + 1) * INFER_LEN]
-            stp = st_all[k].data_ptr()
-            L.check(self.lib.vda_scale_shift(cur.data_ptr(), ref.data_ptr(), ALIGN_LEN * fe, scratch.data_ptr(), stp, 3, s),
-                    "vda_scale_shift")
-            L.check(self.lib.vda_blend(out[pos - INTERP_LEN].data_ptr(), cur[ALIGN_LEN].data_ptr(), stp, INTERP_LEN, fe, s),
-                    "vda_blend")
-            L.check(self.lib.vda_scale_clamp(cur[OVERLAP].data_ptr(), out[pos].data_ptr(), stp, FRAME_STEP * fe, s),
-                    "vda_scale_clamp")
-            L.check(self.lib.vda_scale_clamp(cur[KEYFRAMES[1]].data_ptr(), ref[1].data_ptr(), stp, fe, s), "vda_scale_clamp")
-            pos += FRAME_STEP
-        self.last_scale_shift = st_all
-        return out[:n_frames]
-
-    # ------------------------------------------------------------------ whole job
-    def run(self, frames, input_size=518, return_device=False):
-        n = frames.shape[0]
-        fh, fw = frames[0].shape[:2]
-        isz = effective_input_size(fh, fw, input_size)
-        nh, nw = network_size(fh, fw, isz)
-        idx = window_index_map(n)
+    def _world(self):
+        if self.group is None:
+            return 1, 0
         dist = torch.distributed
-        world = dist.get_world_size() if self.distributed and dist.is_available() and dist.is_initialized() else 1
-        rank = dist.get_rank() if world > 1 else 0
-        first, count = shard_windows(idx.shape[0], world)[rank]
-        mine = idx[first:first + count]
-        if world == 1 and self.streaming:
-            with torch.cuda.device(self.device), torch.no_grad():
-                return self._run_streaming(frames, n, idx, nh, nw, fh, fw, return_device)
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
-        with torch.cuda.device(self.device), torch.no_grad():
-            ev[0].record()
-            if count > 0:
-                ids = np.unique(mine)
-                rowmap, pre = self.preprocess(frames, ids, nh, nw)
-                ev[1].record()
-                raw = self.forward_windows(pre, rowmap, mine, nh, nw, fh, fw)
-                del pre
-            else:
-                ev[1].record()
-                raw = torch.empty((0, fh, fw), dtype=torch.float32, device=self.device)
-            ev[2].record()
-            if world > 1:
-                raw = self._gather_raw(raw, idx.shape[0], world, rank, fh, fw)
-                if rank != 0:
-                    return None
-            ev[3].record()
-            depth = self.stitch(raw, n)
-            ev[4].record()
-            if return_device:
-                return depth
-            t0 = time.perf_counter()
-            host = self._download(depth)
-            # device-side stage times of this call (CUDA events on the launching stream) + the final D2H wall time
-            self.last_stage_s = {"upload_preprocess": ev[0].elapsed_time(ev[1]) / 1e3, "forward_windows": ev[1].elapsed_time(ev[2]) / 1e3,
-                                 "gather": ev[2].elapsed_time(ev[3]) / 1e3, "stitch": ev[3].elapsed_time(ev[4]) / 1e3,
-                                 "d2h": time.perf_counter() - t0}
-            return host
+        return dist.get_world_size(self.group), dist.get_rank(self.group)
 
-    # ------------------------------------------------------------------ single-rank streaming pipeline
-    def _upload_preprocess(self, frames, lo, hi, pre, nh, nw):
-        """Source frames [lo, hi) -> pre[lo:hi] (pre-processing runs once per source frame)."""
+    # ------------------------------------------------------------------ upload + pre-processing
+    def _to_device_u8(self, frames, lo, hi):
+        """Source frames [lo, hi) as a device uint8 tensor [hi-lo, H, W, 3] (no copy when they already are one)."""
+        if isinstance(frames, torch.Tensor):
+            if frames.dtype != torch.uint8:
+                raise TypeError("frames must be uint8 [N,H,W,3]")
+            part = frames[lo:hi]
+            return part if part.device == self.device and part.is_contiguous() else part.contiguous().to(self.device, non_blocking=True)
+        if isinstance(frames, np.ndarray) and frames.flags.c_contiguous:
+            host = frames[lo:hi]
+        else:
+            host = np.ascontiguousarray(np.stack([np.asarray(frames[i]) for i in range(lo, hi)]))
+        if host.dtype != np.uint8:
+            raise TypeError("frames must be uint8 [N,H,W,3]")
+        return torch.from_numpy(host).to(self.device, non_blocking=True)
+
+    def _upload_preprocess(self, frames, lo, hi, pre, nh, nw, row0=None):
+        """Source frames [lo, hi) -> pre[row0 : row0 + hi - lo] (util/transform.py:109-158 + video_depth.py:361; once per
+        source frame).  row0 defaults to lo."""
         fh, fw = frames[0].shape[:2]
         st = L.stream_ptr()
+        row0 = lo if row0 is None else row0
         for c0 in range(lo, hi, self.upload_chunk):
             c1 = min(hi, c0 + self.upload_chunk)
-            if isinstance(frames, np.ndarray) and frames.flags.c_contiguous:
-                host = frames[c0:c1]
-            else:
-                host = np.ascontiguousarray(np.stack([np.asarray(frames[i]) for i in range(c0, c1)]))
-            if host.dtype != np.uint8:
-                raise TypeError("frames must be uint8 [N,H,W,3]")
-            dev = torch.from_numpy(host).to(self.device, non_blocking=True)
-            L.check(self.lib.vda_preprocess_u8(dev.data_ptr(), pre[c0].data_ptr(), c1 - c0, fh, fw, nh, nw, st), "vda_preprocess_u8")
+            dev = self._to_device_u8(frames, c0, c1)
+            L.check(self.lib.vda_preprocess_u8(dev.data_ptr(), pre[row0 + c0 - lo].data_ptr(), c1 - c0, fh, fw, nh, nw, st),
+                    "vda_preprocess_u8")
             del dev
 
-    def _run_streaming(self, frames, n, idx, nh, nw, fh, fw, return_device):
-        """Window k's upload + pre-processing is issued while window k-1 computes (the host copy overlaps the queued
-        kernels), every window is stitched as soon as it is done (the (scale, shift) recurrence is sequential in window
-        order anyway, video_depth.py:379-413), and frames that can no longer change are copied to pinned host memory on
-        a side stream while later windows run.  Same arithmetic, same order, as the batch path."""
-        bf16 = not self.fp32
-        plan = self.model.plan(1, INFER_LEN, nh, nw, self.device, bf16, self.skip_tmp_block)
-        n_win = idx.shape[0]
-        fe = fh * fw
-        total = INFER_LEN + FRAME_STEP * (n_win - 1)
-        s = L.stream_ptr()
-        main = torch.cuda.current_stream()
-        pre = torch.empty((n, 3, nh, nw), dtype=torch.float32, device=self.device)
-        out = torch.empty((total, fh, fw), dtype=torch.float32, device=self.device)
-        raw = torch.empty((2, INFER_LEN, fh, fw), dtype=torch.float32, device=self.device)  # ring: window k -> slot k & 1
-        ref = torch.empty((2, fh, fw), dtype=torch.float32, device=self.device)
-        st_all = torch.zeros((n_win, 2), dtype=torch.float32, device=self.device)
-        st_all[0, 0] = 1.0
-        scratch = torch.zeros(5, dtype=torch.float64, device=self.device)
-        sel_all = torch.as_tensor(idx, dtype=torch.int64).to(self.device)
-        host = None
-        copy_stream = None
-        if not return_device:
-            # device -> pinned staging (cached on the model: page-locking 1 GB costs ~0.5 s) -> the caller's pageable
-            # array, the second hop on a worker thread while the GPU keeps computing
-            host = self._pinned_staging(n * fe * 4).view(torch.float32)[:n * fe].view(n, fh, fw)
-            host_np = host.numpy()
-            result = np.empty((n, fh, fw), dtype=np.float32)
-            copy_stream = torch.cuda.Stream(device=self.device)
-            jobs = queue.Queue()
+    # ------------------------------------------------------------------ whole job
+    def run(self, frames, input_size=518, return_device=False, fresh=True):
+        """frames: uint8 [N, H, W, 3] -- a numpy array (page-locked memory makes the uploads asynchronous), any object with
+        `.shape[0]` and `frames[i]` (what the reference requires, video_depth.py:350), or a torch uint8 tensor (on this
+        device: nothing is uploaded).
 
-            def drain():
-                while True:
-                    job = jobs.get()
-                    if job is None:
-                        return
-                    ev, lo, hi = job
-                    ev.synchronize()
-                    np.copyto(result[lo:hi], host_np[lo:hi])
+        Returns the aligned depth [N, H, W] fp32:
+          * return_device: this rank's final frames as a device tensor -- the whole stack in order for a single rank; for a
+            sharded run the frames of `self.last_frame_ranges` = [(first_frame, count, row)] (nothing crosses PCIe);
+          * single rank: a numpy array -- fresh (reference semantics) or, with fresh=False, a view of the driver's cached
+            page-locked buffer that the next call overwrites;
+          * sharded: group rank 0 gets a numpy view of the host buffer shared by the ranks (valid until the next sharded call
+            on this model), the other ranks get None."""
+        n = int(frames.shape[0])
+        fh, fw = (int(v) for v in frames[0].shape[:2])
+        isz = effective_input_size(fh, fw, input_size)
+        nh, nw = network_size(fh, fw, isz)
+        world, rank = self._world()
+        with torch.cuda.device(self.device), torch.no_grad():
+            return self._run_pipeline(frames, n, fh, fw, nh, nw, world, rank, return_device, fresh)
 
-            worker = threading.Thread(target=drain, daemon=True)
-            worker.start()
-        uploaded = 0
-        copied = 0
+    def _run_pipeline(self, frames, n, fh, fw, nh, nw, world, rank, return_device, fresh):
+        lib, dev = self.lib, self.device
+        dist = torch.distributed
         t_begin = time.perf_counter()
-        for k in range(n_win):
-            need = int(idx[k].max()) + 1
-            if need > uploaded:
-                self._upload_preprocess(frames, uploaded, need, pre, nh, nw)
-                uploaded = need
-            cur = raw[k & 1]
-            torch.index_select(pre, 0, sel_all[k], out=plan.x_in)
-            plan.launch()
-            L.check(self.lib.vda_resize_depth(plan.depth.data_ptr(), L.F32, cur.data_ptr(), INFER_LEN, nh, nw, fh, fw, s),
-                    "vda_resize_depth")
-            if k == 0:
-                out[:INFER_LEN].copy_(cur)
-                ref[0].copy_(cur[KEYFRAMES[0]])
-                ref[1].copy_(cur[KEYFRAMES[1]])
-                pos = INFER_LEN
-            else:
-                stp = st_all[k].data_ptr()
-                L.check(self.lib.vda_scale_shift(cur.data_ptr(), ref.data_ptr(), ALIGN_LEN * fe, scratch.data_ptr(), stp, 3, s),
-                        "vda_scale_shift")
-                L.check(self.lib.vda_blend(out[pos - INTERP_LEN].data_ptr(), cur[ALIGN_LEN].data_ptr(), stp, INTERP_LEN, fe, s),
-                        "vda_blend")
-                L.check(self.lib.vda_scale_clamp(cur[OVERLAP].data_ptr(), out[pos].data_ptr(), stp, FRAME_STEP * fe, s),
-                        "vda_scale_clamp")
-                L.check(self.lib.vda_scale_clamp(cur[KEYFRAMES[1]].data_ptr(), ref[1].data_ptr(), stp, fe, s), "vda_scale_clamp")
-                pos += FRAME_STEP
-            if host is not None:
-                final = n if k == n_win - 1 else min(n, pos - INTERP_LEN)  # the last 8 frames are still to be cross-faded
-                if final > copied:
-                    done = torch.cuda.Event()
-                    done.record(main)
-                    copy_stream.wait_event(done)
-                    with torch.cuda.stream(copy_stream):
-                        host[copied:final].copy_(out[copied:final], non_blocking=True)
-                        landed = torch.cuda.Event()
-                        landed.record(copy_stream)
-                    jobs.put((landed, copied, final))
-                    copied = final
-        self.last_scale_shift = st_all
-        if host is None:
-            return out[:n]
-        jobs.put(None)
-        worker.join()
-        main.synchronize()
-        self.last_stage_s = {"streaming_total": time.perf_counter() - t_begin}
-        return result
+        idx = window_index_map(n)
+        n_win = idx.shape[0]
+        mine = rank_windows(n_win, world, rank)
+        rounds = (n_win + world - 1) // world
+        fe = fh * fw
+        plan = self.model.plan(1, INFER_LEN, nh, nw, dev, not self.fp32, self.skip_tmp_block)
 
+        main = torch.cuda.current_stream()
+        up, side = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        start = torch.cuda.Event()
+        start.record(main)
+        up.wait_event(start)
+        side.wait_event(start)
+
+        # ---- the rank's pool of pre-processed frames and the per-window pointer rows into it
+        rowmap, runs = upload_runs([idx[k] for k in mine])
+        pre = torch.empty((max(1, len(rowmap)), 3, nh, nw), dtype=torch.float32, device=dev)
+        fbytes = 3 * nh * nw * 4
+        if mine:
+            table = torch.tensor([[pre.data_ptr() + rowmap[int(i)] * fbytes for i in idx[k]] for k in mine], dtype=torch.int64)
+            table = table.to(dev, non_blocking=True)
+
+        def alloc(shape):
+            return torch.empty(shape, dtype=torch.float32, device=dev)
+
+        gather = None
+        if world > 1:
+            def gather(dst, src):
+                dist.all_gather_into_tensor(dst.flatten(0, 1), src, group=self.group)   # rank r's 11 frames -> dst[r]
+        ops = CudaStitchOps(lib, fe, dev)
+        stitcher = WindowStitcher(ops, n, world, rank, (fh, fw), alloc, gather)
+        stitcher.st.zero_()
+        stitcher.st[:, 0] = 1.0
+        raw = alloc((2, INFER_LEN, fh, fw))                       # round j -> slot j & 1
+        my_frames = sum(max(0, min(final_range(k, n_win)[1], n) - final_range(k, n_win)[0]) for k in mine)
+        out = alloc((max(1, my_frames) + INFER_LEN, fh, fw))      # this rank's final frames, in processing order
+
+        # ---- where the result goes
+        host = host_np = result = worker = jobs = None
+        if not return_device:
+            if world > 1:
+                host = self._shared_result(n * fe * 4).view(torch.float32)[:n * fe].view(n, fh, fw)
+            else:
+                host = self._pinned_staging(n * fe * 4).view(torch.float32)[:n * fe].view(n, fh, fw)
+            host_np = host.numpy()
+            if world == 1 and fresh:
+                # device -> page-locked staging -> the caller's fresh pageable array, the second hop on a worker thread
+                # while the GPU keeps computing
+                result = np.empty((n, fh, fw), dtype=np.float32)
+                jobs = queue.Queue()
+
+                def drain():
+                    while True:
+                        job = jobs.get()
+                        if job is None:
+                            return
+                        ev, lo, hi = job
+                        ev.synchronize()
+                        np.copyto(result[lo:hi], host_np[lo:hi])
+
+                worker = threading.Thread(target=drain, daemon=True)
+                worker.start()
+
+        def upload(j):
+            with torch.cuda.stream(up):
+                for (first, count, row0) in runs[j]:
+                    self._upload_preprocess(frames, first, first + count, pre, nh, nw, row0=row0)
+                ev = torch.cuda.Event()
+                ev.record(up)
+            return ev
+
+        timed = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+        ev_round = [None] * rounds
+        marks = []       # (fwd0, fwd1, x0, x1, s1, d1) per round
+        ranges = []
+        pos = 0
+        ev_up = upload(0) if mine else None
+        try:
+            for j in range(rounds):
+                k = mine[j] if j < len(mine) else None
+                m = {}
+                if k is not None:
+                    main.wait_event(ev_up)
+                    if j >= 2:
+                        main.wait_event(ev_round[j - 2])   # raw / send slot j & 1 was last read by round j - 2's stitch
+                    s = main.cuda_stream
+                    m["f0"] = timed()
+                    m["f0"].record(main)
+                    L.check(lib.vda_copy_frames(table.data_ptr() + j * INFER_LEN * 8, plan.src_ptrs.data_ptr(), None, None, 1,
+                                                INFER_LEN * 8, s), "vda_copy_frames")
+                    plan.launch()
+                    cur = raw[j & 1]
+                    L.check(lib.vda_resize_depth(plan.depth.data_ptr(), L.F32, cur.data_ptr(), INFER_LEN, nh, nw, fh, fw, s),
+                            "vda_resize_depth")
+                    send = stitcher.send_buffer(j)
+                    # the frames the other ranks need, resized straight into the exchange buffer (0, 1 | 12 | 24..31)
+                    for dst0, slot0, cnt in ((0, 0, ALIGN_LEN), (XCHG_REF, KEYFRAMES[1], 1),
+                                             (XCHG_REF + 1, INFER_LEN - INTERP_LEN, INTERP_LEN)):
+                        L.check(lib.vda_resize_depth(plan.depth[slot0].data_ptr(), L.F32, send[dst0].data_ptr(), cnt, nh, nw, fh,
+                                                     fw, s), "vda_resize_depth")
+                    m["f1"] = timed()
+                    m["f1"].record(main)
+                    side.wait_event(m["f1"])
+                    if j + 1 < len(mine):
+                        ev_up = upload(j + 1)
+                with torch.cuda.stream(side):
+                    m["x0"] = timed()
+                    m["x0"].record(side)
+                    stitcher.exchange(j)
+                    m["x1"] = timed()
+                    m["x1"].record(side)
+                    done = stitcher.round(j, raw[j & 1] if k is not None else None, out[pos:])
+                    m["s1"] = timed()
+                    m["s1"].record(side)
+                    if done is not None and done[1] > 0:
+                        lo, cnt = done
+                        ranges.append((lo, cnt, pos))
+                        if host is not None:
+                            host[lo:lo + cnt].copy_(out[pos:pos + cnt], non_blocking=True)
+                            if jobs is not None:
+                                landed = torch.cuda.Event()
+                                landed.record(side)
+                                jobs.put((landed, lo, lo + cnt))
+                        pos += cnt
+                    m["d1"] = timed()
+                    m["d1"].record(side)
+                    ev_round[j] = m["d1"]
+                marks.append(m)
+        finally:
+            # give the plan its own input frames back (`forward()` reads x_in through the same pointer array)
+            L.check(lib.vda_copy_frames(plan.src_ptrs_default.data_ptr(), plan.src_ptrs.data_ptr(), None, None, 1, INFER_LEN * 8,
+                                        main.cuda_stream), "vda_copy_frames")
+        main.wait_stream(side)
+        main.wait_stream(up)
+        self.last_scale_shift = stitcher.st
+        self.last_frame_ranges = ranges
+        if return_device:
+            self._stage_times(marks, t_begin, stitcher, sync=False)
+            return out[:n] if world == 1 else out[:pos]
+        if jobs is not None:
+            jobs.put(None)
+            worker.join()
+        main.synchronize()
+        if world > 1:
+            dist.barrier(self.group)   # every rank's frames have landed in the shared buffer
+        self._stage_times(marks, t_begin, stitcher, sync=True)
+        if world > 1:
+            return host_np if rank == 0 else None
+        return result if result is not None else host_np
+
+    def _stage_times(self, marks, t_begin, stitcher, sync):
+        """Device-side stage times of this call from CUDA events on the launching streams (summed over the rank's rounds)."""
+        info = {"rounds": len(marks), "exchange_bytes_per_round": stitcher.exchange_bytes_per_round}
+        if sync:
+            f = x = s = d = 0.0
+            for m in marks:
+                if "f0" in m:
+                    f += m["f0"].elapsed_time(m["f1"])
+                x += m["x0"].elapsed_time(m["x1"])
+                s += m["x1"].elapsed_time(m["s1"])
+                d += m["s1"].elapsed_time(m["d1"])
+            info.update(forward_s=f / 1e3, exchange_s=x / 1e3, stitch_s=s / 1e3, d2h_s=d / 1e3, total_s=time.perf_counter() - t_begin)
+        self.last_stage_s = info
+
+    # ------------------------------------------------------------------ host buffers
     def _download(self, depth, chunk_frames=32, workers=4):
-        """Device [n, H, W] fp32 -> a fresh pageable numpy array.  A plain `.cpu()` into pageable memory moves ~2 GB/s (the
-        runtime stages through small internal buffers and the page faults of the new array land on one thread); here the
-        stack goes to the cached page-locked staging buffer in chunks on a side stream at PCIe rate while worker threads
-        copy finished chunks out (numpy releases the GIL for the memcpy, the first-touch faults spread over the threads)."""
+        """Device [n, H, W] fp32 -> a fresh pageable numpy array (used by the streaming mode).  A plain `.cpu()` into
+        pageable memory moves ~2 GB/s (the runtime stages through small internal buffers and the page faults of the new
+        array land on one thread); here the stack goes to the cached page-locked staging buffer in chunks on a side stream
+        at PCIe rate while worker threads copy finished chunks out (numpy releases the GIL for the memcpy, the first-touch
+        faults spread over the threads)."""
         n, fh, fw = depth.shape
         if n == 0:
             return np.empty((0, fh, fw), dtype=np.float32)
@@ -357,27 +515,41 @@ class WindowedDepthDriver:
             self.model._vda_pinned_staging = buf
         return buf
 
-    def _gather_raw(self, raw, n_win, world, rank, fh, fw):
-        return gather_window_blocks(raw, n_win, world, rank)
+    def _shared_result(self, nbytes):
+        """The node-wide result buffer of a sharded run: shared memory mapped by every rank of the group and page-locked in
+        each process, so that every rank's device->host copies are asynchronous DMA over its own PCIe link.  Cached on the
+        model (creating and page-locking gigabytes costs seconds) and grown on demand; all ranks call this together."""
+        hit = getattr(self.model, "_vda_shared_result", None)
+        if hit is None or hit.tensor.numel() < nbytes:
+            if hit is not None:
+                hit.release()
+            hit = SharedHostBuffer(nbytes, self.group, self.lib)
+            self.model._vda_shared_result = hit
+        return hit.tensor
 
 
-def gather_window_blocks(raw, n_win, world, rank):
-    """Raw depth blocks of every rank -> rank 0, point-to-point (NCCL over NVLink on GPUs; the same code runs over gloo
-    in the CPU tests).  Block sizes follow from `shard_windows`, so no size exchange is needed.  Returns the full
-    [n_win*32, H, W] stack on rank 0 and the local block elsewhere."""
-    dist = torch.distributed
-    shards = shard_windows(n_win, world)
-    if rank == 0:
-        full = torch.empty((n_win * INFER_LEN,) + tuple(raw.shape[1:]), dtype=raw.dtype, device=raw.device)
-        full[:raw.shape[0]].copy_(raw)
-        reqs = []
-        for r in range(1, world):
-            lo, cnt = shards[r]
-            if cnt:
-                reqs.append(dist.irecv(full[lo * INFER_LEN:(lo + cnt) * INFER_LEN], src=r))
-        for q in reqs:
-            q.wait()
-        return full
-    if raw.shape[0]:
-        dist.send(raw.contiguous(), dst=0)
-    return raw
+class SharedHostBuffer:
+    """Shared memory mapped by every rank of `group`, page-locked in this process (released explicitly or on collection:
+    a mapping must never go away while the CUDA runtime still holds it registered)."""
+
+    def __init__(self, nbytes, group, lib):
+        self.lib = lib
+        self.mm = open_shared_buffer(nbytes, group)
+        self.tensor = torch.frombuffer(self.mm, dtype=torch.uint8)
+        self.registered = lib.vda_host_register(self.tensor.data_ptr(), nbytes) == 0
+        if not self.registered:
+            warnings.warn("video_depth_anything_b200: page-locking the shared result buffer failed ("
+                          f"{lib.vda_last_error().decode(errors='replace')}); device->host copies into it will be staged by the "
+                          "runtime", RuntimeWarning)
+
+    def release(self):
+        if self.registered:
+            torch.cuda.synchronize()
+            self.lib.vda_host_unregister(self.tensor.data_ptr())
+            self.registered = False
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass

@@ -21,6 +21,25 @@ from .modules import ENCODERS
 
 KPAD_PATCH = 640  # 3*14*14 = 588 padded to a multiple of the 64-wide K block
 
+_graph_fallback_warned = False
+
+
+def _warn_graph_fallback(exc):
+    """CUDA-graph capture of a launch list failed: the plan keeps running as a loop of launches (same results, more host
+    time per window).  Said once per process so that a silent slow path cannot hide in a benchmark."""
+    global _graph_fallback_warned
+    if not _graph_fallback_warned:
+        _graph_fallback_warned = True
+        import warnings
+        warnings.warn(f"video_depth_anything_b200: CUDA graph capture failed ({type(exc).__name__}: {exc}); "
+                      "falling back to per-kernel launches", RuntimeWarning, stacklevel=3)
+
+
+def active_toggles():
+    """The VDA_* environment switches that change numerics or the execution path, as set in this process (recorded in
+    bench lines)."""
+    return {k: v for k, v in sorted(os.environ.items()) if k.startswith("VDA_")}
+
 
 def _conv3x3_pack(w: torch.Tensor) -> torch.Tensor:
     """[Cout, Cin, 3, 3] -> [Cout, 9*Cin], k = (dy*3+dx)*Cin + ci."""
@@ -295,6 +314,12 @@ class ForwardPlan:
         M = BT * ntok
         lib = self._lib
         self.x_in = torch.empty((BT, 3, self.H, self.W), dtype=torch.float32, device=self.device)
+        # The patch embed reads frame f at src_ptrs[f] (a device array, read when the kernel runs).  By default these are
+        # the frames of x_in; the sliding-window driver points them at its pool of once-pre-processed frames instead, per
+        # window, so a window's inputs (video_depth.py:358-364) are gathered without a copy, also under graph replay.
+        fbytes = 3 * self.H * self.W * 4
+        self.src_ptrs_default = torch.tensor([self.x_in.data_ptr() + f * fbytes for f in range(BT)], dtype=torch.int64).to(self.device)
+        self.src_ptrs = self.src_ptrs_default.clone()
 
         # ---- position embedding for this resolution (dinov2.py:179-210): identity at 518x518, else bicubic
         if P == 37 * 37 and self.H == self.W:
@@ -309,7 +334,7 @@ class ForwardPlan:
         # ---- patch embed (patch_embed.py:76-78) + cls + pos (dinov2.py:212-221)
         a_pe = self.buf("im2col", BT * P, KPAD_PATCH)
         resid = self.buf("resid", M, D, torch.float32)
-        self.op(lib.vda_im2col_patch, self.x_in.data_ptr(), a_pe.data_ptr(), self.dcode, BT, self.H, self.W, KPAD_PATCH)
+        self.op(lib.vda_im2col_patch_frames, self.src_ptrs.data_ptr(), a_pe.data_ptr(), self.dcode, BT, self.H, self.W, KPAD_PATCH)
         self.op(lib.vda_cls_rows, resid.data_ptr(), W_["cls"].data_ptr(), pos.data_ptr(), BT, ntok, D)
         self.gemm(a_pe, W_["patch.w"], BT * P, D, KPAD_PATCH, geo=(BT, ph, pwid), bias=W_["patch.b"], resid=resid, pos=pos,
                   resid_map=L.MAP_TOKENS, resid_assign=1, pos_rows=ntok)
@@ -573,8 +598,9 @@ class ForwardPlan:
                 with torch.cuda.graph(g):
                     self._launch_ops()
                 self._graph = g
-            except Exception:  # capture is an optimisation: stay on the launch loop if the runtime refuses
+            except Exception as e:  # capture is an optimisation: stay on the launch loop if the runtime refuses
                 self.use_graph = False
+                _warn_graph_fallback(e)
 
     def _launch_ops(self):
         st = L.stream_ptr()
@@ -729,8 +755,9 @@ class StreamPlan(ForwardPlan):
                 with torch.cuda.graph(g):
                     self._launch_ops()
                 st["graph"] = g
-            except Exception:  # capture is an optimisation
+            except Exception as e:  # capture is an optimisation
                 self.use_graph = False
+                _warn_graph_fallback(e)
 
     def launch(self):
         raise RuntimeError("StreamPlan runs stage by stage (run_stage)")

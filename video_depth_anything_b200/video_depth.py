@@ -10,6 +10,9 @@ bf16 tensor-core build runs and reproduces autocast's rounding points; without a
 """
 from __future__ import annotations
 
+import collections
+import warnings
+
 import numpy as np
 import torch
 import torch.nn as nn
@@ -43,7 +46,12 @@ class VideoDepthAnything(nn.Module):
         self.pretrained = DinoV2Params(encoder)
         self.head = DPTHeadTemporalParams(self.pretrained.embed_dim, features, list(out_channels), num_frames, pe)
         self._packed = {}   # (device, bf16) -> (version key, PackedWeights)
-        self._plans = {}    # (device, bf16, B, T, H, W, skip) -> ForwardPlan
+        # (device, bf16, B, T, H, W, skip, ...) -> plan, least recently used first.  A plan owns every activation buffer of
+        # its shape (vitl 518x518: ~20 GB), so the cache is capped: callers that walk over many resolutions (app.py,
+        # eval loops) evict the oldest plan instead of exhausting the GPU.
+        self._plans = collections.OrderedDict()
+        self.max_plans = 4
+        self._fp16_autocast_noted = False
         self.force_simt = False  # tests: run the bf16 build on the SIMT kernels instead of tcgen05
         self.attn_simt = False   # tests: tcgen05 GEMMs but the exact-rounding SIMT attention
 
@@ -56,48 +64,56 @@ class VideoDepthAnything(nn.Module):
         ver = self._weights_version()
         hit = self._packed.get(key)
         if hit is None or hit[0] != ver:
-            self._plans = {k: v for k, v in self._plans.items() if (k[0], k[1]) != key}
+            self._plans = collections.OrderedDict((k, v) for k, v in self._plans.items() if (k[0], k[1]) != key)
             self._packed[key] = (ver, PackedWeights(self, device, bf16))
         return self._packed[key][1]
+
+    def _cached_plan(self, key, build):
+        p = self._plans.get(key)
+        if p is None:
+            while len(self._plans) >= max(1, int(self.max_plans)):
+                self._plans.popitem(last=False)   # drop the least recently used plan; its buffers go back to the allocator
+            p = build()
+            self._plans[key] = p
+        else:
+            self._plans.move_to_end(key)
+        return p
 
     def plan(self, B, T, H, W, device, bf16, skip_tmp_block=False, keep=()):
         pw = self._packed_weights(device, bf16)
         use_tc = bf16 and not self.force_simt
         key = (str(device), bf16, B, T, H, W, bool(skip_tmp_block), use_tc, self.attn_simt, tuple(sorted(keep)))
-        p = self._plans.get(key)
-        if p is None:
-            p = ForwardPlan(pw, B, T, H, W, device, skip_tmp_block, use_tc=use_tc, keep=keep, attn_tc=use_tc and not self.attn_simt)
-            self._plans[key] = p
-        return p
+        return self._cached_plan(key, lambda: ForwardPlan(pw, B, T, H, W, device, skip_tmp_block, use_tc=use_tc, keep=keep,
+                                                          attn_tc=use_tc and not self.attn_simt))
 
     def head_plan(self, B, T, H, W, device, bf16, skip_tmp_block=False, keep=()):
         """Plan of the head alone (taps in, depth out) for x of [B, T, 3, H, W]."""
         pw = self._packed_weights(device, bf16)
         use_tc = bf16 and not self.force_simt
         key = (str(device), bf16, "head", B, T, H, W, bool(skip_tmp_block), use_tc, tuple(sorted(keep)))
-        p = self._plans.get(key)
-        if p is None:
-            p = HeadPlan(pw, B, T, H, W, device, skip_tmp_block, use_tc=use_tc, keep=keep, attn_tc=use_tc)
-            self._plans[key] = p
-        return p
+        return self._cached_plan(key, lambda: HeadPlan(pw, B, T, H, W, device, skip_tmp_block, use_tc=use_tc, keep=keep, attn_tc=use_tc))
 
     def stream_plan(self, T, H, W, device, bf16, rows, npreds, skip_tmp_block=False, enc_batch=1):
         """Plan of the streaming mode for one (context length, network size, store size, prediction counts)."""
         pw = self._packed_weights(device, bf16)
         key = (str(device), bf16, "stream", T, H, W, int(rows), tuple(npreds), bool(skip_tmp_block), self.force_simt, self.attn_simt,
                int(enc_batch))
-        p = self._plans.get(key)
-        if p is None:
-            p = StreamPlan(pw, T, H, W, device, rows, npreds, skip_tmp_block, use_tc=bf16 and not self.force_simt,
-                           attn_tc=bf16 and not self.force_simt and not self.attn_simt, enc_batch=enc_batch)
-            self._plans[key] = p
-        return p
+        return self._cached_plan(key, lambda: StreamPlan(pw, T, H, W, device, rows, npreds, skip_tmp_block,
+                                                         use_tc=bf16 and not self.force_simt,
+                                                         attn_tc=bf16 and not self.force_simt and not self.attn_simt,
+                                                         enc_batch=enc_batch))
 
     # ------------------------------------------------------------------ forward (video_depth.py:58-65)
     def forward(self, x, skip_tmp_block=False):
         B, T, Cc, H, W = x.shape
         L.require_device(x.device)
-        bf16 = torch.is_autocast_enabled("cuda") if hasattr(torch, "is_autocast_enabled") else False
+        bf16 = torch.is_autocast_enabled("cuda")
+        if bf16 and torch.get_autocast_dtype("cuda") == torch.float16 and not self._fp16_autocast_noted:
+            # the reference's `infer_video_depth(fp32=False)` enters a dtype-less autocast, i.e. fp16 on CUDA
+            # (video_depth.py:367); this library has one reduced-precision build, bf16 (BASELINE.json north_star)
+            self._fp16_autocast_noted = True
+            warnings.warn("video_depth_anything_b200: CUDA autocast dtype is float16; the bf16 build runs instead "
+                          "(wider exponent, 3 fewer mantissa bits) -- see INTEGRATION.md", RuntimeWarning, stacklevel=2)
         plan = self.plan(B, T, H, W, x.device, bf16, skip_tmp_block)
         depth = plan.run(x.to(torch.float32).flatten(0, 1))
         # fp32 in both builds: under CUDA autocast the head's bilinear upsample is an fp32 op, so the output convs and
@@ -121,6 +137,37 @@ class VideoDepthAnything(nn.Module):
 
     # ------------------------------------------------------------------ driver (video_depth.py:329-417)
     def infer_video_depth(self, frames, target_fps, input_size=518, device="cuda", fp32=False, skip_tmp_block=False):
+        """Same arguments and return value as the reference.  Runs in this process only, whatever torch.distributed state
+        exists (one video per rank under torchrun behaves like the reference); `infer_video_depth_sharded` splits ONE video
+        over the ranks of a process group."""
         drv = WindowedDepthDriver(self, device=device, fp32=fp32, skip_tmp_block=skip_tmp_block)
         depth = drv.run(frames, input_size)
+        return depth, target_fps
+
+    def infer_video_depth_sharded(self, frames, target_fps, input_size=518, device="cuda", fp32=False, skip_tmp_block=False,
+                                  group=None, return_device=False):
+        """One video over the GPUs of a node: every rank of `group` (default: the world group; one
+        process per GPU, same node) calls this with the same `frames`, of which it reads only the frames its own windows
+        touch.  Window k runs on rank k % world; the ranks exchange 11 frames per window over NCCL, each stitches its own
+        windows (bit-identical to a single-rank run) and copies them to a host buffer shared by the ranks.
+
+        Returns (depth, target_fps): on group rank 0 `depth` is the [N, H, W] fp32 result as a numpy view of that shared
+        page-locked buffer -- valid until the next sharded call on this model, copy it to keep it; on the other ranks it
+        is None.  With return_device nothing is copied to the host: every rank gets its own final frames as a device
+        tensor (`WindowedDepthDriver.last_frame_ranges` names them).  The ranks must agree on the frame count and size
+        (checked)."""
+        dist = torch.distributed
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("infer_video_depth_sharded needs an initialised torch.distributed process group")
+        group = dist.group.WORLD if group is None else group
+        drv = WindowedDepthDriver(self, device=device, fp32=fp32, skip_tmp_block=skip_tmp_block, group=group)
+        # the exchange sizes follow from the video geometry: refuse to start (instead of hanging in a collective) when the
+        # ranks were handed different videos
+        mine = [int(frames.shape[0])] + [int(v) for v in frames[0].shape[:2]] + [int(input_size)]
+        seen = [None] * dist.get_world_size(group)
+        dist.all_gather_object(seen, mine, group=group)
+        if any(v != mine for v in seen):
+            raise ValueError(f"infer_video_depth_sharded: ranks disagree on (frames, H, W, input_size): {seen}")
+        self._last_driver = drv
+        depth = drv.run(frames, input_size, return_device=return_device)
         return depth, target_fps
