@@ -273,7 +273,8 @@ def test_attention_simt(mode):
         assert stats("attn_simt_f32", o.reshape(frames, ntok, heads, 64).permute(0, 2, 1, 3), ref)["max_rel_to_peak"] < 1e-5
     # temporal attention (motion_module/attention.py:182-211)
     for (T, hw, C_) in ((4, 6, 64), (32, 5, 192), (32, 3, 1024), (16, 4, 256), (3, 7, 384), (32, 9, 256), (64, 3, 256), (64, 2, 1024),
-                       (32, 7, 64), (16, 6, 64), (64, 3, 192), (32, 4, 384)):
+                       (32, 7, 64), (16, 6, 64), (64, 3, 192), (32, 4, 384),
+                       (1, 5, 64), (5, 4, 192), (10, 3, 256), (24, 5, 1024), (33, 2, 64), (50, 3, 256)):   # any T <= 64
         batch = 2 if T == 4 else 1
         qkv = (torch.randn(batch * T * hw, 3 * C_, device=dev)).to(dt)
         o = torch.zeros(batch * T * hw, C_, device=dev, dtype=dt)

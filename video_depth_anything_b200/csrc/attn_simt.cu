@@ -84,7 +84,9 @@ __global__ void __launch_bounds__(128) encoder_attn_simt(const T* __restrict__ q
 // ---------------------------------------------------------------- temporal attention
 template <typename T, int TT, bool RB>
 __global__ void __launch_bounds__(256) temporal_attn_kernel(const T* __restrict__ qkv, T* __restrict__ o, int hw, int C,
-                                                           int heads, int hpc, float scale) {
+                                                           int heads, int hpc, float scale, int Tn) {
+  // TT = compile-time capacity (registers, shared memory), Tn <= TT = the frames that exist: any --inference_length /
+  // forward T runs on the next capacity up; key columns j >= Tn score -inf, query rows t >= Tn are idle.
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int d = C / heads;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -93,10 +95,10 @@ __global__ void __launch_bounds__(256) temporal_attn_kernel(const T* __restrict_
   T* Ks = reinterpret_cast<T*>(smem_raw) + (size_t)warp * 2 * TT * d;
   T* Vs = Ks + TT * d;
   const long long ld = 3LL * C;
-  auto row_ptr = [&](int t) { return qkv + (((long long)b * TT + t) * hw + p) * ld + h * d; };
-  // stage K and V of this (token, head): TT rows of d contiguous elements
+  auto row_ptr = [&](int t) { return qkv + (((long long)b * Tn + t) * hw + p) * ld + h * d; };
+  // stage K and V of this (token, head): Tn rows of d contiguous elements
   const int vpr = d >> 3;
-  for (int i = lane; i < TT * vpr; i += 32) {
+  for (int i = lane; i < Tn * vpr; i += 32) {
     int t = i / vpr, c = (i % vpr) * 8;
     const T* rp = row_ptr(t);
     if constexpr (sizeof(T) == 2) {
@@ -116,7 +118,7 @@ __global__ void __launch_bounds__(256) temporal_attn_kernel(const T* __restrict_
 #pragma unroll
   for (int qq = 0; qq < NQ; ++qq) {
     const int t = qq * 32 + lane;
-    const bool active = t < TT;
+    const bool active = t < Tn;
     const T* qp = row_ptr(active ? t : 0);
     float s[TT];
 #pragma unroll
@@ -126,16 +128,18 @@ __global__ void __launch_bounds__(256) temporal_attn_kernel(const T* __restrict_
       Vec8<T>::load(qp + c, q8);
 #pragma unroll
       for (int j = 0; j < TT; ++j) {
-        float k8[8];
-        Vec8<T>::load(Ks + j * d + c, k8);
+        if (j < Tn) {
+          float k8[8];
+          Vec8<T>::load(Ks + j * d + c, k8);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) s[j] = fmaf(q8[i], k8[i], s[j]);
+          for (int i = 0; i < 8; ++i) s[j] = fmaf(q8[i], k8[i], s[j]);
+        }
       }
     }
     float mx = -INFINITY;
 #pragma unroll
     for (int j = 0; j < TT; ++j) {
-      s[j] = R<RB>(scale * s[j]);  // baddbmm(alpha=scale) output dtype
+      s[j] = j < Tn ? R<RB>(scale * s[j]) : -INFINITY;  // baddbmm(alpha=scale) output dtype
       mx = fmaxf(mx, s[j]);
     }
     float sum = 0.f;
@@ -146,15 +150,17 @@ __global__ void __launch_bounds__(256) temporal_attn_kernel(const T* __restrict_
     }
 #pragma unroll
     for (int j = 0; j < TT; ++j) s[j] = R<RB>(s[j] / sum);
-    T* op = o + (((long long)b * TT + (active ? t : 0)) * hw + p) * C + h * d;
+    T* op = o + (((long long)b * Tn + (active ? t : 0)) * hw + p) * C + h * d;
     for (int c = 0; c < d; c += 8) {
       float a8[8] = {};
 #pragma unroll
       for (int j = 0; j < TT; ++j) {
-        float v8[8];
-        Vec8<T>::load(Vs + j * d + c, v8);
+        if (j < Tn) {
+          float v8[8];
+          Vec8<T>::load(Vs + j * d + c, v8);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) a8[i] = fmaf(s[j], v8[i], a8[i]);
+          for (int i = 0; i < 8; ++i) a8[i] = fmaf(s[j], v8[i], a8[i]);
+        }
       }
       if (active) {
 #pragma unroll
@@ -349,7 +355,7 @@ int launch_temporal_mma(const void* qkv, void* o, int batch, int hw, int C, int 
 }
 
 template <typename T, int TT, bool RB>
-int launch_temporal(const void* qkv, void* o, int batch, int hw, int C, int heads, cudaStream_t st) {
+int launch_temporal(const void* qkv, void* o, int batch, int hw, int C, int heads, cudaStream_t st, int Tn) {
   const int d = C / heads;
   int hpc = heads;
   while (hpc > 1 && (size_t)hpc * 2 * TT * d * sizeof(T) > 96 * 1024) hpc >>= 1;
@@ -363,7 +369,7 @@ int launch_temporal(const void* qkv, void* o, int batch, int hw, int C, int head
     }
   }
   dim3 grid(batch * hw, heads / hpc);
-  kern<<<grid, hpc * 32, smem, st>>>((const T*)qkv, (T*)o, hw, C, heads, hpc, 1.0f / sqrtf((float)d));
+  kern<<<grid, hpc * 32, smem, st>>>((const T*)qkv, (T*)o, hw, C, heads, hpc, 1.0f / sqrtf((float)d), Tn);
   VDA_CUDA_LAUNCH_CHECK("temporal_attn_kernel");
   return 0;
 }
@@ -450,18 +456,14 @@ extern "C" int vda_temporal_attention(const void* qkv, void* o, int32_t dtype, i
     return launch_temporal_mma<64>(qkv, o, batch, hw, C, heads, st);
   }
 #define TA(TT)                                                                              \
-  return bf ? launch_temporal<bf16, TT, true>(qkv, o, batch, hw, C, heads, st)              \
-            : launch_temporal<float, TT, false>(qkv, o, batch, hw, C, heads, st)
-  switch (T) {
-    case 1: TA(1);
-    case 2: TA(2);
-    case 3: TA(3);
-    case 4: TA(4);
-    case 8: TA(8);
-    case 16: TA(16);
-    case 32: TA(32);
-    case 64: TA(64);
-    default: VDA_CHECK_ARG(false, "vda_temporal_attention: T=%d not in {1,2,3,4,8,16,32,64}", T);
-  }
+  return bf ? launch_temporal<bf16, TT, true>(qkv, o, batch, hw, C, heads, st, T)           \
+            : launch_temporal<float, TT, false>(qkv, o, batch, hw, C, heads, st, T)
+  // any T in [1, 64] (the reference accepts any --inference_length, run.py:35): the SIMT kernel at the next capacity up
+  VDA_CHECK_ARG(T >= 1 && T <= 64, "vda_temporal_attention: T=%d not in [1, 64]", T);
+  if (T <= 4) TA(4);
+  if (T <= 8) TA(8);
+  if (T <= 16) TA(16);
+  if (T <= 32) TA(32);
+  TA(64);
 #undef TA
 }
