@@ -83,9 +83,13 @@ def encoder_taps(sd, x: torch.Tensor, encoder: str, collect=None):
         collect["tokens0"] = t
     taps = []
     for i in range(enc["depth"]):
+        if collect is not None and collect.get("want_blocks"):
+            collect[f"blk{i}_in"] = t
         t = encoder_block(sd, f"{p}blocks.{i}.", t, enc["heads"])
         if i in enc["taps"]:
             taps.append(t)
+    if collect is not None and collect.get("want_blocks"):
+        collect[f"blk{enc['depth']}_in"] = t
     D = t.shape[-1]
     taps = [F.layer_norm(o, (D,), sd[p + "norm.weight"], sd[p + "norm.bias"], 1e-6)[:, 1:] for o in taps]
     if collect is not None:
@@ -287,9 +291,14 @@ def head_forward(sd, taps, ph: int, pw: int, T: int, skip_tmp_block: bool = Fals
     l3r = F.conv2d(l3, sd[sc + "layer3_rn.weight"], None, padding=1)
     l4r = F.conv2d(l4, sd[sc + "layer4_rn.weight"], None, padding=1)
     p4 = _fusion(sd, sc + "refinenet4.", l4r, None, l3r.shape[2:])
+    if collect is not None:
+        collect["l1r"], collect["l2r"], collect["l3r"], collect["l4r"] = l1r, l2r, l3r, l4r
+        collect["path_4_pre"] = p4   # refinenet4's output, before motion module 2
     if not skip_tmp_block:
         p4 = temporal_module(sd, h + "motion_modules.2.", p4, T)
     p3 = _fusion(sd, sc + "refinenet3.", p4, l3r, l2r.shape[2:])
+    if collect is not None:
+        collect["path_3_pre"] = p3   # refinenet3's output, before motion module 3
     p3 = temporal_module(sd, h + "motion_modules.3.", p3, T)
     p2 = _fusion(sd, sc + "refinenet2.", p3, l2r, l1r.shape[2:])
     p1 = _fusion(sd, sc + "refinenet1.", p2, l1r, None)

@@ -147,13 +147,24 @@ def _gen(name: str, seed: int) -> torch.Generator:
     return g
 
 
-def make_state_dict(encoder: str, seed: int = 0, num_frames: int = 32, pe: str = "ape") -> "OrderedDict[str, torch.Tensor]":
+def make_state_dict(encoder: str, seed: int = 0, num_frames: int = 32, pe: str = "ape",
+                    style: str = "random") -> "OrderedDict[str, torch.Tensor]":
     """The fixed-seed weight recipe, fp32 CPU tensors.
 
     Weights ~ N(0, g/sqrt(fan_in)); biases ~ N(0, 0.05); every norm gets a
     non-trivial affine; LayerScale gamma ~ U(0.5, 1.5); proj_out is *not* zero;
     the last 1x1 conv is mostly positive so the depth map is not half zeros.
+
+    style="random" (the goldens): every residual branch is as large as the stream it is added to, so a 12 / 24-block
+    encoder amplifies one flipped bf16 rounding into an independent realisation of the network.
+    style="trained_like": the statistics of a trained checkpoint instead -- LayerScale gamma ~ 0.1 x U(0.5, 1.5) (DINOv2
+    initialises it at 1e-5 and trains it up to a fraction of one), softmax logits without the extra gain, motion-module
+    `proj_out` (zero-initialised in the reference, motion_module.py:61-62) at a quarter of the random scale: each branch
+    is a perturbation of its residual stream, as in a trained network, and rounding noise averages instead of
+    amplifying.  Everything else is identical; every branch of the path stays live.
     """
+    assert style in ("random", "trained_like")
+    smooth = style == "trained_like"
     sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
     for name, shape in param_spec(encoder, num_frames, pe).items():
         g = _gen(name, seed)
@@ -162,6 +173,8 @@ def make_state_dict(encoder: str, seed: int = 0, num_frames: int = 32, pe: str =
             t = sinusoidal_pe(shape[1], shape[2])
         elif leaf == "gamma":
             t = torch.rand(shape, generator=g) + 0.5
+            if smooth:
+                t = t * 0.1
         elif leaf in ("cls_token", "pos_embed"):
             t = torch.randn(shape, generator=g) * 0.02
         elif leaf == "mask_token":
@@ -182,9 +195,11 @@ def make_state_dict(encoder: str, seed: int = 0, num_frames: int = 32, pe: str =
                     fan_in *= d
             gain = 1.0
             if name.endswith("attn.qkv.weight") or name.endswith("to_q.weight") or name.endswith("to_k.weight"):
-                gain = 1.3  # peakier softmax than the trunc_normal(0.02) default
+                gain = 1.0 if smooth else 1.3  # peakier softmax than the trunc_normal(0.02) default
             if "resConfUnit" in name or "output_conv" in name or "_rn." in name:
                 gain = 1.4  # ReLU-fed convs: keep the signal alive through the fusion stack
+            if smooth and ".proj_out." in name:
+                gain = 0.25
             t = torch.randn(shape, generator=g) * (gain / math.sqrt(fan_in))
             if name.endswith("output_conv2.2.weight"):
                 t = t.abs() * 0.8 + t * 0.2

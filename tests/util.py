@@ -43,20 +43,24 @@ def bf16_close(name, got, ref, ulps=2.0, frac=1e-3):
     return s
 
 
-def bf16_gate(name, ours, ref_bf16, ref_f32):
-    """Whole-network gate of the bf16 build (BASELINE.json north_star: rel-err <= 1e-2 and AbsRel <= 1e-3 against the
-    reference's autocast output).
+def bf16_gate(name, ours, ref_bf16, ref_f32, mean_factor=1.5):
+    """Whole-network ACCURACY gate of the bf16 build -- not the north-star tolerance, which is printed beside it.
 
-    Two bf16 executions of a 12/24-block network only agree bit-for-bit when every fp32 accumulation happens in the same
-    order; cuBLAS/cuDNN and the tcgen05 kernels here sum in different orders, a rounding flips somewhere in the first
-    block, and from there on the two runs are independent bf16 realisations of the same network.  On the seeded random
-    weights the reference's OWN autocast output sits 2-3e-2 (max) / 3-5e-3 (mean) away from its fp32 output (measured
-    on the B200, see DESIGN.md "bf16 parity"), so 1e-2 / 1e-3 between two such realisations is below the reference's
-    own noise floor.  The gate therefore is: the stated tolerance, or the reference's own bf16 deviation from fp32 when
-    that is larger --
-      (a) accuracy:  err(ours, fp32)  <= max(1e-2, 2 x err(ref_bf16, fp32)) at the max (a noisy statistic), max(1e-3, 1.5 x) at the mean
-      (b) agreement: err(ours, ref_bf16) <= max(1e-2, 2 x err(ref_bf16, fp32)) at the max; AbsRel <= max(1e-3, 2 x)
-    Rounding-point fidelity itself is pinned kernel by kernel (test_gpu_kernels.py / test_gpu_tc.py, <= 2 bf16 ulps)."""
+    BASELINE.json states rel-err <= 1e-2 and AbsRel <= 1e-3 against the reference's autocast output.  The reference does
+    not meet that against itself: the same reference arithmetic with its GEMMs merely batched differently lands 3e-3 (mean)
+    / 3e-2 (max) away (tests/test_gpu_parity.py measures it: a few percent of every bf16 layer's outputs sit close enough
+    to a rounding boundary for another fp32 summation order to flip them by one bf16 ulp, and ~20 layers of that add up).
+    The strict figures are therefore REPORTED -- "strict gate NOT met" where they are not -- and what is asserted is that
+    the bf16 build is as accurate as the reference's own bf16 arithmetic, measured against the reference's fp32 output:
+      (a) accuracy:  err(ours, fp32)  <= max(1e-2, 2 x err(ref_bf16, fp32)) at the max (one pixel: a noisy statistic),
+                                      <= max(1e-3, mean_factor x err(ref_bf16, fp32)) at the mean -- 1.2 where the network is
+                                      not chaotic (trained-like weights); 1.5 with the random recipe, whose 12 / 24 blocks
+                                      amplify each run's per-block rounding error (equal to the reference's, stage by stage:
+                                      tests/test_gpu_parity.py) by a factor that varies from input to input
+      (b) agreement: err(ours, ref_bf16) <= max(1e-2, 2 x err(ref_bf16, fp32)) at the max; AbsRel <= max(1e-3, 2 x) -- two
+          independent bf16 evaluations differ by about sqrt(2) x the deviation of either from the fp32 result
+    Rounding-point fidelity itself is pinned stage by stage with teacher-forced inputs (tests/test_gpu_parity.py) and kernel
+    by kernel (test_gpu_kernels.py / test_gpu_tc.py, <= 2 bf16 ulps)."""
     e_ref, e_ours, e_x = rel_err_map(ref_bf16, ref_f32), rel_err_map(ours, ref_f32), rel_err_map(ours, ref_bf16)
     ar_ref, ar_x = abs_rel(ref_bf16, ref_f32), abs_rel(ours, ref_bf16)
     r = dict(ref_max=e_ref.max().item(), ref_mean=e_ref.mean().item(), ours_max=e_ours.max().item(),
@@ -64,10 +68,10 @@ def bf16_gate(name, ours, ref_bf16, ref_f32):
     strict = r["x_max"] <= 1e-2 and ar_x <= 1e-3
     print(f"[{name}] ours-vs-ref_bf16 max {r['x_max']:.3e} mean {r['x_mean']:.3e} AbsRel {ar_x:.3e} | ref_bf16-vs-fp32 max "
           f"{r['ref_max']:.3e} mean {r['ref_mean']:.3e} AbsRel {ar_ref:.3e} | ours-vs-fp32 max {r['ours_max']:.3e} mean "
-          f"{r['ours_mean']:.3e} | strict 1e-2/1e-3 gate {'met' if strict else 'below the reference noise floor'}")
+          f"{r['ours_mean']:.3e} | strict 1e-2/1e-3 gate {'met' if strict else 'NOT met (nor by the reference against itself)'}")
     assert np.isfinite(r["x_max"]) and np.isfinite(r["ours_max"]), name
     assert r["ours_max"] <= max(1e-2, 2.0 * r["ref_max"]), (name, r)
-    assert r["ours_mean"] <= max(1e-3, 1.5 * r["ref_mean"]), (name, r)
+    assert r["ours_mean"] <= max(1e-3, mean_factor * r["ref_mean"]), (name, r)
     assert r["x_max"] <= max(1e-2, 2.0 * r["ref_max"]), (name, r)
     assert ar_x <= max(1e-3, 2.0 * ar_ref), (name, r)
     return r

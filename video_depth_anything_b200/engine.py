@@ -209,6 +209,7 @@ class ForwardPlan:
         self.BT = batch * T
         self.ph, self.pw_ = H // 14, W // 14
         self.ops = []      # (callable, args) in launch order
+        self.marks = {}    # stage name -> index of its first op (stage-by-stage parity tests run `run_range` between marks)
         self.bufs = {}     # name -> tensor (kept alive; `keep` names are exposed for tap-level tests)
         self.keep = set(keep)
         self.n_launches = 0
@@ -288,6 +289,18 @@ class ForwardPlan:
         self.n_launches += 1 if d.use_tc else 2
         return d
 
+    def mark(self, name):
+        self.marks[self._prefix + name] = len(self.ops)
+
+    def run_range(self, first, last):
+        """Launch ops[first:last] on the current stream (tests: one stage of the network on caller-written inputs)."""
+        keep = self.ops
+        self.ops = keep[first:last]
+        try:
+            self._launch_ops()
+        finally:
+            self.ops = keep
+
     def op(self, fn, *args, launches=1):
         self.ops.append((fn, list(args)))
         self.n_launches += launches
@@ -348,6 +361,7 @@ class ForwardPlan:
         hid = self.buf("hid", M, 4 * D)
         taps = []
         for i in range(pw.depth):
+            self.mark(f"blk{i}")
             self.layernorm(resid, y, W_[f"b{i}.norm1.w"], W_[f"b{i}.norm1.b"], 1e-6, M, D)
             self.gemm(y, W_[f"b{i}.qkv.w"], M, 3 * D, D, bias=W_[f"b{i}.qkv.b"], out=qkv)
             self.op(lib.vda_attention, qkv.data_ptr(), att.data_ptr(), self.dcode, BT, ntok, pw.heads, int(self.bf16),
@@ -357,10 +371,12 @@ class ForwardPlan:
             self.gemm(y, W_[f"b{i}.fc1.w"], M, 4 * D, D, bias=W_[f"b{i}.fc1.b"], act=L.ACT_GELU, out=hid)
             self.gemm(hid, W_[f"b{i}.fc2.w"], M, D, 4 * D, bias=W_[f"b{i}.fc2.b"], resid=resid, gamma=W_[f"b{i}.ls2"])
             if i in pw.taps:
+                self.mark(f"tapnorm{len(taps)}")
                 t = self.buf(f"tap{len(taps)}", BT * P, D)
                 # final norm on the tap, class token dropped (dinov2.py:309-312)
                 self.layernorm(resid, t, W_["norm.w"], W_["norm.b"], 1e-6, M, D, group_rows=ntok, skip_first=1)
                 taps.append(t)
+        self.mark("enc_end")
         return taps
 
     # ------------------------------------------------------------------ motion module (motion_module.py:108-133,173-186)
@@ -513,10 +529,13 @@ class ForwardPlan:
         BT = self.BT
         h2, w2, h3, w3 = 2 * ph, 2 * pwid, ph, pwid
         h4, w4 = (ph + 1) // 2, (pwid + 1) // 2
+        self.mark("mm0")
         l3m = self.padded("mm0", h3, w3, oc[2])
         self._motion_module(0, l3, (h3, w3), oc[2], l3m, L.MAP_PADDED)
+        self.mark("mm1")
         l4m = self.padded("mm1", h4, w4, oc[3])
         self._motion_module(1, l4, (h4, w4), oc[3], l4m, L.MAP_PADDED)
+        self.mark("rn34_f4")
         rn3, rn3_relu = self._rn(3, l3m, h3, w3)
         rn4, rn4_relu = self._rn(4, l4m, h4, w4)
         if skip_tmp_block:
@@ -525,10 +544,13 @@ class ForwardPlan:
         else:
             p4d = self.buf("path_4d", BT * h3 * w3, F)
             self._fusion(4, rn4, rn4_relu, None, None, h4, w4, h3, w3, p4d, L.MAP_SAME)
+            self.mark("mm2")
             p4 = self.padded("path_4", h3, w3, F)
             self._motion_module(2, p4d, (h3, w3), F, p4, L.MAP_PADDED)
+        self.mark("f3")
         p3d = self.buf("path_3d", BT * h2 * w2, F)
         self._fusion(3, p4, None, rn3, rn3_relu, h3, w3, h2, w2, p3d, L.MAP_SAME)
+        self.mark("mm3")
         if split_mm3:
             att, hbuf = self._mm_front(3, p3d, (h2, w2), F)
             return att, hbuf, p3d
@@ -542,13 +564,16 @@ class ForwardPlan:
         pw, W_, lib = self.pw, self.pw.w, self._lib
         BT, ph, pwid, F = self.BT, self.ph, self.pw_, pw.features
         h1, w1, h2, w2 = 4 * ph, 4 * pwid, 2 * ph, 2 * pwid
+        self.mark("rn12_f2")
         rn1, rn1_relu = self._rn(1, l1, h1, w1)
         rn2, rn2_relu = self._rn(2, l2, h2, w2)
         p2 = self.padded("path_2", h1, w1, F)
         self._fusion(2, p3, None, rn2, rn2_relu, h2, w2, h1, w1, p2, L.MAP_PADDED)
+        self.mark("f1")
         h0, w0 = 2 * h1, 2 * w1
         p1 = self.padded("path_1", h0, w0, F)
         self._fusion(1, p2, None, rn1, rn1_relu, h1, w1, h0, w0, p1, L.MAP_PADDED)
+        self.mark("out")
         # output_conv1 -> bilinear to (14ph, 14pw) -> fp32 island output_conv2 (dpt_temporal.py:91-99)
         o1 = self.buf("oc1", BT * h0 * w0, F // 2)
         self.conv3x3(p1, "oc1.w", h0, w0, F, F // 2, bias=W_["oc1.b"], out=o1, out_map=L.MAP_DENSE)
@@ -572,9 +597,11 @@ class ForwardPlan:
         return depth
 
     def _build_head(self, taps, skip_tmp_block):
+        self.mark("reassemble")
         l1, l2, l3, l4 = self._reassemble(taps)
         p3 = self._head_middle(l3, l4, skip_tmp_block)
         self.depth = self._head_tail(p3, l1, l2)
+        self.mark("end")
 
     # ------------------------------------------------------------------ execution
     def run(self, x: torch.Tensor) -> torch.Tensor:
