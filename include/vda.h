@@ -193,6 +193,17 @@ int vda_output_head_f16(const void* x, const void* w_f16, const float* bias, con
                         float* depth, int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow,
                         vda_stream_t stream);
 
+/* The form the bf16 build runs: fp16 operands where they are safe, TF32 where they are not, decided on the device.
+ * A range guard first sets *flag (device int32) when any element of x is beyond +-6e4 or non-finite (the interpolated
+ * operands are convex combinations of x, so they stay inside the same range); the fp16-operand kernel returns at once
+ * when the flag is set, the TF32 kernel (fp32's exponent range: what the reference's island computes under cuDNN's
+ * defaults, dpt_temporal.py:95-97) returns at once when it is clear and otherwise recomputes the whole launch.  No host
+ * synchronisation; the caller may read *flag afterwards to learn which form produced `depth`.  The caller checks ONCE
+ * that the weights themselves fit fp16 (max |w| <= 6e4) before choosing this entry point. */
+int vda_output_head_guarded(const void* x, const void* w_f16, const float* w_f32, const float* bias, const float* head_w,
+                            float head_b, float* depth, int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh,
+                            int32_t ow, int32_t* flag, vda_stream_t stream);
+
 /* Patch-embed im2col (patch_embed.py:76): x[frames,3,H,W] f32 -> A[frames*(H/14)*(W/14), kpad] (k = c*196+i*14+j; pad = 0). */
 int vda_im2col_patch(const float* x, void* A, int32_t a_dtype, int32_t frames, int32_t H, int32_t W, int32_t kpad,
                      vda_stream_t stream);

@@ -4,8 +4,8 @@
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 TAG=${1:-r01}
-ARGS="--steps 1 --warmup 3 --no-cpu-baseline"
-timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err || { echo "bench failed"; tail -5 gpurun_out/bench_$TAG.err; exit 1; }
+ARGS="--steps 1 --warmup 3 --no-cpu-baseline --no-video --no-eager"
+timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-video --no-eager > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err || { echo "bench failed"; tail -5 gpurun_out/bench_$TAG.err; exit 1; }
 cat gpurun_out/bench_$TAG.json | cut -c1-600
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 550 -c 600 --csv \
   --log-file gpurun_out/launches_$TAG.csv python bench.py $ARGS > gpurun_out/ncu_launches_$TAG.log 2>&1

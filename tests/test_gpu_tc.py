@@ -227,3 +227,57 @@ def test_output_head_fused_f16(Ci, ih, iw, oh, ow, frames):
                                     ih, iw, Ci, oh, ow, L.stream_ptr()), "vda_output_head_f16")
     torch.cuda.synchronize()
     assert torch.isfinite(depth).all()
+
+
+@pytest.mark.parametrize("Ci,ih,iw,oh,ow,frames", [(128, 32, 48, 56, 84, 3), (64, 9, 7, 21, 13, 1)])
+def test_output_head_guarded_falls_back_to_tf32_outside_fp16_range(Ci, ih, iw, oh, ow, frames):
+    """vda_output_head_guarded: in range it IS the fp16-operand kernel (bit-identical, flag clear); with activations beyond
+    fp16's range (where vda_output_head_f16 alone saturates at +-65504 and returns wrong values) the device-side guard
+    selects the TF32 kernel -- bit-identical to vda_output_head, and right against fp64 torch.  No host synchronisation
+    decides anything."""
+    from video_depth_anything_b200.engine import _conv3x3_pack
+    L, lib = _lib()
+    torch.manual_seed(Ci + oh + 1)
+    x = torch.randn(frames, Ci, ih, iw, device=dev).bfloat16()
+    w = torch.randn(32, Ci, 3, 3, device=dev) / (9 * Ci) ** 0.5
+    b, hw_, hb = torch.randn(32, device=dev) * 0.1, torch.randn(32, device=dev).abs(), 0.05
+    wp = _conv3x3_pack(w)
+    wh = wp.to(torch.float16).contiguous()
+    flag = torch.full((1,), 7, dtype=torch.int32, device=dev)
+    st = L.stream_ptr()
+
+    def run(xin):
+        xd = xin.permute(0, 2, 3, 1).reshape(-1, Ci).contiguous()
+        outs = [torch.full((frames, oh, ow), float("nan"), device=dev) for _ in range(3)]
+        L.check(lib.vda_output_head_guarded(xd.data_ptr(), wh.data_ptr(), wp.data_ptr(), b.data_ptr(), hw_.data_ptr(), hb,
+                                            outs[0].data_ptr(), frames, ih, iw, Ci, oh, ow, flag.data_ptr(), st), "guarded")
+        L.check(lib.vda_output_head_f16(xd.data_ptr(), wh.data_ptr(), b.data_ptr(), hw_.data_ptr(), hb, outs[1].data_ptr(), frames,
+                                        ih, iw, Ci, oh, ow, st), "f16")
+        L.check(lib.vda_output_head(xd.data_ptr(), wp.data_ptr(), b.data_ptr(), hw_.data_ptr(), hb, outs[2].data_ptr(), frames, ih,
+                                    iw, Ci, oh, ow, st), "tf32")
+        torch.cuda.synchronize()
+        up = F.interpolate(xin.double(), (oh, ow), mode="bilinear", align_corners=True)
+        ref = F.relu(F.conv2d(F.relu(F.conv2d(up, w.double(), b.double(), padding=1)), hw_.double().reshape(1, 32, 1, 1),
+                              torch.tensor([hb], device=dev, dtype=torch.float64)))
+        return outs, ref.reshape(frames, oh, ow), int(flag.item())
+
+    (g, h, t), ref, fl = run(x)
+    assert fl == 0 and torch.equal(g, h) and not torch.equal(g, t)
+    # one element far outside fp16's range, the rest as before: the whole launch is recomputed in TF32
+    x2 = x.clone()
+    x2[0, 3, ih // 2, iw // 2] = 3.0e5
+    (g, h, t), ref, fl = run(x2)
+    assert fl == 1 and torch.equal(g, t)
+    s = stats("head_guarded_out_of_range", g, ref)
+    assert s["max_rel_to_peak"] < 2e-3
+    assert stats("head_f16_saturated", h, ref)["max_rel_to_peak"] > 0.05   # what the unguarded fp16 form would have returned
+    # the same with every activation large, with an infinity, and with a NaN: always the TF32 kernel's result
+    (g, h, t), ref, fl = run((x.float() * 3e4).bfloat16())
+    assert fl == 1 and torch.equal(g, t) and stats("head_guarded_all_large", g, ref)["max_rel_to_peak"] < 2e-3
+    x3 = x.clone()
+    x3[0, 0, 0, 0] = float("inf")
+    (g, h, t), _, fl = run(x3)
+    assert fl == 1 and torch.equal(g.nan_to_num(1.0, 2.0, 3.0), t.nan_to_num(1.0, 2.0, 3.0))
+    # back in range: the flag is cleared by the call itself
+    (g, h, t), ref, fl = run(x)
+    assert fl == 0 and torch.equal(g, h)

@@ -64,6 +64,11 @@ struct HtArgs {
   float head_b, rh, rw;
   int frames, ih, iw, C, oh, ow;
   int tiles_x, tiles_y, total_tiles, ngroups, nkc;
+  // range guard of the fp16-operand form (vda_output_head_guarded): *flag != 0 means some input is outside fp16's range.
+  // skip_if_set: this launch returns at once when the flag is set (the fp16 kernel); run_if_set: it returns at once when
+  // the flag is clear (the TF32 kernel that recomputes the frame set in that case).  NULL: unconditional.
+  const int* skip_if_set;
+  const int* run_if_set;
 };
 
 // K-major, no swizzle: LBO = distance between core matrices along K, SBO = distance between 8-row groups along M.
@@ -94,6 +99,9 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
   float* spar = reinterpret_cast<float*>(smem + OFF_PAR);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int KC = H ? 64 : 32;  // channels per chunk
+  // grid-uniform early outs of the guarded form (the flag was written by an earlier kernel on this stream)
+  if (a.skip_if_set != nullptr && *a.skip_if_set != 0) return;
+  if (a.run_if_set != nullptr && *a.run_if_set == 0) return;
 
   if (threadIdx.x == 0) {
     if (ptx::smem_u32(smem) & 1023) {
@@ -330,9 +338,27 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
 
 }  // namespace
 
+// flag |= any |x| > limit or non-finite.  One pass over the map (bf16, 16 B per thread and iteration).
+__global__ void __launch_bounds__(256) range_guard_kernel(const uint4* __restrict__ x, long long nvec, float limit,
+                                                         int* __restrict__ flag) {
+  bool bad = false;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+    const uint4 v = x[i];
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      // !(|x| <= limit) is true for values beyond the limit, infinities and NaNs alike
+      bad |= !(fabsf(bf16lo_to_f32(w[k])) <= limit);
+      bad |= !(fabsf(bf16hi_to_f32(w[k])) <= limit);
+    }
+  }
+  if (__syncthreads_or(bad) && threadIdx.x == 0) atomicOr(flag, 1);
+}
+
 template <bool H>
 static int launch_head(const void* x, const void* w, const float* bias, const float* head_w, float head_b, float* depth,
-                       int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow, vda_stream_t stream) {
+                       int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh, int32_t ow, vda_stream_t stream,
+                       const int* skip_if_set = nullptr, const int* run_if_set = nullptr) {
   constexpr int KC = H ? 64 : 32, ES = H ? 2 : 4;
   VDA_CHECK_ARG(C >= KC && C % KC == 0, "vda_output_head%s: C=%d must be a multiple of %d", H ? "_f16" : "", C, KC);
   VDA_CHECK_ARG(frames > 0 && ih > 0 && iw > 0 && oh > 0 && ow > 0, "vda_output_head: bad geometry");
@@ -352,6 +378,8 @@ static int launch_head(const void* x, const void* w, const float* bias, const fl
   a.total_tiles = frames * a.tiles_x * a.tiles_y;
   a.ngroups = (a.total_tiles + GROUP - 1) / GROUP;
   a.nkc = C / KC;
+  a.skip_if_set = skip_if_set;
+  a.run_if_set = run_if_set;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t ce = cudaFuncSetAttribute(head_tail_kernel<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, HT_SMEM);
@@ -377,4 +405,34 @@ extern "C" int vda_output_head_f16(const void* x, const void* w_f16, const float
                                    float* depth, int32_t frames, int32_t ih, int32_t iw, int32_t C, int32_t oh,
                                    int32_t ow, vda_stream_t stream) {
   return launch_head<true>(x, w_f16, bias, head_w, head_b, depth, frames, ih, iw, C, oh, ow, stream);
+}
+
+// fp16 operands where they are safe, TF32 where they are not -- decided on the device, no host synchronisation:
+//   1. range guard: *flag = any |x| > 6e4 or non-finite in the output_conv1 map (one extra read of the bf16 map; the
+//      interpolation is a convex combination of its inputs, so the interpolated operands are inside the same range);
+//   2. the fp16-operand kernel, which returns at once when the flag is set;
+//   3. the TF32 kernel (fp32's exponent range, dpt_temporal.py:95-97 under cuDNN's defaults), which returns at once when
+//      the flag is clear and otherwise computes the whole launch.
+// Three launches, graph-capturable; the common case costs the guard's pass and one empty launch.
+extern "C" int vda_output_head_guarded(const void* x, const void* w_f16, const float* w_f32, const float* bias,
+                                       const float* head_w, float head_b, float* depth, int32_t frames, int32_t ih,
+                                       int32_t iw, int32_t C, int32_t oh, int32_t ow, int32_t* flag, vda_stream_t stream) {
+  VDA_CHECK_ARG(flag != nullptr && ((uintptr_t)x % 16) == 0, "vda_output_head_guarded: flag is NULL or x is not 16B aligned");
+  const long long count = (long long)frames * ih * iw * C;
+  VDA_CHECK_ARG(count % 8 == 0, "vda_output_head_guarded: element count must be a multiple of 8");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  cudaError_t ce = cudaMemsetAsync(flag, 0, sizeof(int), st);
+  if (ce != cudaSuccess) {
+    vda_set_error("vda_output_head_guarded: memset failed: %s", cudaGetErrorString(ce));
+    return (int)ce;
+  }
+  const long long nvec = count / 8;
+  long long blocks = (nvec + 256 * 4 - 1) / (256 * 4);
+  if (blocks > 8LL * vda_sm_count()) blocks = 8LL * vda_sm_count();
+  if (blocks < 1) blocks = 1;
+  range_guard_kernel<<<(unsigned)blocks, 256, 0, st>>>(reinterpret_cast<const uint4*>(x), nvec, 6.0e4f, flag);
+  VDA_CUDA_LAUNCH_CHECK("range_guard_kernel");
+  int rc = launch_head<true>(x, w_f16, bias, head_w, head_b, depth, frames, ih, iw, C, oh, ow, stream, flag, nullptr);
+  if (rc) return rc;
+  return launch_head<false>(x, w_f32, bias, head_w, head_b, depth, frames, ih, iw, C, oh, ow, stream, nullptr, flag);
 }

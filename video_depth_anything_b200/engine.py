@@ -147,6 +147,10 @@ class PackedWeights:
         w2 = _conv3x3_pack(sd[sc + "output_conv2.0.weight"]).float()
         w["oc2.w32"] = w2.contiguous()
         w["oc2.w16"] = w2.to(torch.float16).contiguous()  # operands of vda_output_head_f16 (round to nearest, 10-bit mantissa like TF32)
+        # fp16 operands only when the WEIGHTS fit fp16: no overflow, and the absolute rounding step of fp16's subnormal
+        # range (2^-25) negligible against the largest weight (the activations are range-checked on the device, per launch)
+        wmax = float(w2.abs().max().item())
+        self.oc2_fp16_safe = bool(torch.isfinite(w2).all().item()) and 1e-3 <= wmax <= 6.0e4
         vec("oc2.b", sd[sc + "output_conv2.0.bias"])
         vec("oc2.hw", sd[sc + "output_conv2.2.weight"].reshape(32))
         self.head_b = float(sd[sc + "output_conv2.2.bias"].reshape(()).item())
@@ -583,10 +587,19 @@ class ForwardPlan:
         self.bufs[self._prefix + "depth"] = depth
         if self.use_tc and self.fused_tail and (F // 2) % 32 == 0:
             # bf16 build: interpolation, TF32 tensor-core conv and the ReLU -> 1x1 -> ReLU tail in one kernel
-            half = (F // 2) % 64 == 0 and os.environ.get("VDA_HEAD_TF32", "0") != "1"
-            self.op(lib.vda_output_head_f16 if half else lib.vda_output_head, o1.data_ptr(),
-                    W_["oc2.w16" if half else "oc2.w32"].data_ptr(), W_["oc2.b"].data_ptr(), W_["oc2.hw"].data_ptr(),
-                    float(pw.head_b), depth.data_ptr(), BT, h0, w0, F // 2, self.H, self.W)
+            # fp16 operands (same 10 mantissa bits as TF32, rounded to nearest, half the MMAs) when the weights fit fp16,
+            # behind a device-side range guard on the activations that falls back to the TF32 kernel: nothing saturates
+            # silently (dpt_temporal.py:95-97 runs this conv in fp32 / TF32)
+            half = (F // 2) % 64 == 0 and pw.oc2_fp16_safe and os.environ.get("VDA_HEAD_TF32", "0") != "1"
+            if half:
+                self.head_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+                self.bufs[self._prefix + "head_flag"] = self.head_flag
+                self.op(lib.vda_output_head_guarded, o1.data_ptr(), W_["oc2.w16"].data_ptr(), W_["oc2.w32"].data_ptr(),
+                        W_["oc2.b"].data_ptr(), W_["oc2.hw"].data_ptr(), float(pw.head_b), depth.data_ptr(), BT, h0, w0, F // 2,
+                        self.H, self.W, self.head_flag.data_ptr(), launches=3)
+            else:
+                self.op(lib.vda_output_head, o1.data_ptr(), W_["oc2.w32"].data_ptr(), W_["oc2.b"].data_ptr(), W_["oc2.hw"].data_ptr(),
+                        float(pw.head_b), depth.data_ptr(), BT, h0, w0, F // 2, self.H, self.W)
         else:
             up = self.buf("up", BT * (self.H + 2) * (self.W + 2), F // 2, torch.float32, zero=True)
             self.op(lib.vda_bilinear, o1.data_ptr(), self.dcode, up.data_ptr(), L.F32, BT, h0, w0, 0, self.H, self.W, 1, F // 2)
