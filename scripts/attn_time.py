@@ -1,15 +1,28 @@
-import sys, torch
-sys.path.insert(0, "/root/repo")
-from video_depth_anything_b200 import lib as L
-lib = L.load(); dev = torch.device("cuda:0")
+"""Device time of the tcgen05 flash attention on the encoder's shape (vitl: 32 frames x 1370 tokens x 16 heads).
+VDA_LIB=/path/to/variant.so times an experimental build of the library."""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from video_depth_anything_b200 import lib as L  # noqa: E402
+
+if os.environ.get("VDA_LIB"):
+    L.LIB_PATH = os.environ["VDA_LIB"]
+lib = L.load()
+dev = torch.device("cuda:0")
 frames, ntok, heads = 32, 1370, 16
 qkv = (torch.randn(frames * ntok, 3 * heads * 64, device=dev) * 1.3).bfloat16()
 o = torch.empty(frames * ntok, heads * 64, device=dev, dtype=torch.bfloat16)
-f = lambda: L.check(lib.vda_attention(qkv.data_ptr(), o.data_ptr(), L.BF16, frames, ntok, heads, 1, 1, L.stream_ptr()), "attn")
-for _ in range(3): f()
+f = lambda: L.check(lib.vda_attention(qkv.data_ptr(), o.data_ptr(), L.BF16, frames, ntok, heads, 1, 1, L.stream_ptr()), "attn")  # noqa: E731
+for _ in range(3):
+    f()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
-for _ in range(20): f()
-e1.record(); torch.cuda.synchronize()
-print("attention %.1f us" % (e0.elapsed_time(e1) * 50))
+for _ in range(20):
+    f()
+e1.record()
+torch.cuda.synchronize()
+print("attention %.1f us  (%s)" % (e0.elapsed_time(e1) * 50, os.environ.get("VDA_LIB", "in-tree library")))

@@ -43,7 +43,11 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x
   constexpr int RPW = 32 / LPR;              // rows per warp
   const int lane = threadIdx.x & (LPR - 1);
   const int sub = (threadIdx.x & 31) / LPR;
-  const long long row = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RPW + sub;
+  // Blocks walk the rows from the LAST to the first: the GEMM epilogue that produced x (the fp32 residual stream, larger
+  // than L2) wrote its rows in ascending order, so the tail of x is what L2 still holds when this kernel starts, and the
+  // head of y -- written last here -- is what the next GEMM (ascending again) reads first.
+  const long long blk = (long long)gridDim.x - 1 - blockIdx.x;
+  const long long row = (blk * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RPW + sub;
   const bool live = row < rows;  // dead rows still take part in the shuffles below
   long long orow = row;
   bool emit = live;
