@@ -133,6 +133,43 @@ def test_intermediate_taps_fp32():
     assert stats("path_1", unpad(plan.bufs["path_1"], 8 * ph, 8 * pw), col["path_1"])["max_rel_to_peak"] < 1e-4
 
 
+def test_motion_module_forward_hooks_fire():
+    """The reference's diagnostic harness hooks `model.head.motion_modules[i]` (Test_singleImage_processing.py:132-142):
+    hooks registered on the drop-in fire once per forward with (input, output) of the temporal module as [B, C, T, h, w]."""
+    enc, T, H, W = "vits", 4, 42, 56
+    m, sd = get_model(enc)
+    x = synthetic_clip(1, T, H, W, 6).to(dev)
+    seen = {}
+    handles = [mm.register_forward_hook(lambda mod, inp, out, i=i: seen.__setitem__(i, (inp, out)))
+               for i, mm in enumerate(m.head.motion_modules)]
+    try:
+        with torch.no_grad():
+            m(x)
+    finally:
+        for h in handles:
+            h.remove()
+    col = {}
+    old = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        with torch.no_grad():
+            omodel.forward(sd, x, enc, collect=col)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
+    assert sorted(seen) == [0, 1, 2, 3]
+    for i, (kin, kout) in enumerate([("layer_3", "mm0"), ("layer_4", "mm1"), ("path_4_pre", "path_4"), ("path_3_pre", "path_3")]):
+        (xin, a, b), out = seen[i]
+        assert a is None and b is None and xin.shape == out.shape and xin.dim() == 5 and xin.shape[2] == T
+        ref_in = col[kin].unflatten(0, (1, T)).permute(0, 2, 1, 3, 4)
+        ref_out = col[kout].unflatten(0, (1, T)).permute(0, 2, 1, 3, 4)
+        assert stats(f"hook{i}_in", xin, ref_in)["max_rel_to_peak"] < 1e-4
+        assert stats(f"hook{i}_out", out, ref_out)["max_rel_to_peak"] < 1e-4
+    with torch.no_grad():
+        m(x)   # hooks removed: nothing fires, nothing breaks
+    assert len(seen) == 4
+
+
 def test_forward_contract():
     """Drop-in behaviours: batch > 1, shape assertion, determinism, permutation sensitivity."""
     m, sd = get_model("vits")

@@ -99,12 +99,25 @@ def test_schedule_covers_every_frame_once():
             owned = sorted(k for r in range(world) for k in rank_windows(n_win, world, r))
             assert owned == list(range(n_win))
     assert rank_windows(94, 8, 7) == list(range(7, 94, 8)) and len(rank_windows(94, 8, 5)) == 12
-    # a rank uploads every source frame of its windows exactly once, as runs of consecutive frames
-    idx = window_index_map(2048)
-    rowmap, runs = upload_runs([idx[k] for k in rank_windows(94, 8, 3)])
-    assert sorted(rowmap.values()) == list(range(len(rowmap)))
-    assert sum(c for win in runs for (_, c, _) in win) == len(rowmap) == len(set(int(i) for k in rank_windows(94, 8, 3) for i in idx[k]))
-    assert max(len(win) for win in runs) <= 3
+    # the ring of pre-processed frames: every slot of every window resolves to the row its frame was last uploaded to, a
+    # group is only rewritten three windows later, and frame 0 keeps row 0
+    for world, rank in ((1, 0), (2, 1), (8, 3)):
+        idx = window_index_map(2048)
+        wins = [idx[k] for k in rank_windows(94, world, rank)]
+        runs, slot_rows, pool = upload_runs(wins)
+        assert pool == 97 and len(runs) == len(slot_rows) == len(wins)
+        content = {}   # row -> frame id, replayed in upload order
+        for j, (win, rr, sr) in enumerate(zip(wins, runs, slot_rows)):
+            for first, count, row0 in rr:
+                for t in range(count):
+                    row = row0 + t
+                    assert row == 0 or 1 + (j % 3) * 32 <= row < 1 + (j % 3) * 32 + 32
+                    content[row] = first + t
+            assert [content[r] for r in sr] == [int(i) for i in win]
+            assert max(len(rr), 1) <= 4
+        # a single rank uploads every frame exactly once (22 new frames per window after the first)
+        if world == 1:
+            assert sum(c for rr in runs for (_, c, _) in rr) == 2048
 
 
 @pytest.mark.parametrize("n_frames", [5, 22, 23, 45, 100])

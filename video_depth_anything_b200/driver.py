@@ -92,21 +92,45 @@ def final_range(k: int, n_windows: int):
     return lo, hi
 
 
+POOL_GROUPS = 3   # the frame pool is a ring of three window-sized groups behind one permanent row for frame 0
+
+
 def upload_runs(idx_rows):
-    """For a rank's windows in processing order: the source frames each one has to upload (those not seen before), as runs
-    of consecutive ids, and the pool row of every frame.  Returns (rowmap {id: row}, [[(first_id, count, first_row)]])."""
-    rowmap, per_window = {}, []
-    for row in idx_rows:
-        new = sorted(set(int(i) for i in row) - set(rowmap))
-        runs = []
-        for i in new:
-            rowmap[i] = len(rowmap)
-            if runs and runs[-1][0] + runs[-1][1] == i:
+    """For a rank's windows in processing order: the source frames each one has to upload, as runs of consecutive ids, and
+    the pool row of each of the window's 32 slots.  The pool is a RING, so device memory does not grow with the video: row 0
+    holds frame 0 (slot 0 of every window, video_depth.py:363), window j's new frames go to group j % 3 (32 rows each) and
+    stay valid for window j + 1, which re-reads up to nine of them (its overlap / key-frame slots); group j % 3 is
+    overwritten by window j + 3's upload, which the driver orders after window j + 1's forward.
+    Returns ([[(first_id, count, first_row)] per window], [[row of each slot] per window], pool rows)."""
+    runs_all, rows_all = [], []
+    prev = {}          # id -> row of the frames uploaded for the previous window
+    have0 = False
+    for j, row in enumerate(idx_rows):
+        ids = [int(i) for i in row]
+        need = sorted(set(ids))
+        cur, runs = {}, []
+        base, used = 1 + (j % POOL_GROUPS) * INFER_LEN, 0
+        for i in need:
+            if (i == 0 and have0) or i in prev:
+                continue
+            if i == 0:
+                r = 0
+                have0 = True
+            else:
+                r = base + used
+                used += 1
+                cur[i] = r
+            if runs and runs[-1][0] + runs[-1][1] == i and runs[-1][2] + runs[-1][1] == r:
                 runs[-1][1] += 1
             else:
-                runs.append([i, 1, rowmap[i]])
-        per_window.append([tuple(r) for r in runs])
-    return rowmap, per_window
+                runs.append([i, 1, r])
+        lookup = dict(prev)
+        lookup.update(cur)
+        lookup[0] = 0
+        rows_all.append([lookup[i] for i in ids])
+        runs_all.append([tuple(r) for r in runs])
+        prev = cur
+    return runs_all, rows_all, 1 + POOL_GROUPS * INFER_LEN
 
 
 class WindowStitcher:
@@ -311,12 +335,12 @@ class WindowedDepthDriver:
         up.wait_event(start)
         side.wait_event(start)
 
-        # ---- the rank's pool of pre-processed frames and the per-window pointer rows into it
-        rowmap, runs = upload_runs([idx[k] for k in mine])
-        pre = torch.empty((max(1, len(rowmap)), 3, nh, nw), dtype=torch.float32, device=dev)
+        # ---- the rank's ring of pre-processed frames and the per-window pointer rows into it
+        runs, slot_rows, pool_rows = upload_runs([idx[k] for k in mine])
+        pre = torch.empty((pool_rows, 3, nh, nw), dtype=torch.float32, device=dev)
         fbytes = 3 * nh * nw * 4
         if mine:
-            table = torch.tensor([[pre.data_ptr() + rowmap[int(i)] * fbytes for i in idx[k]] for k in mine], dtype=torch.int64)
+            table = torch.tensor([[pre.data_ptr() + r * fbytes for r in rows] for rows in slot_rows], dtype=torch.int64)
             table = table.to(dev, non_blocking=True)
 
         def alloc(shape):
@@ -332,7 +356,9 @@ class WindowedDepthDriver:
         stitcher.st[:, 0] = 1.0
         raw = alloc((2, INFER_LEN, fh, fw))                       # round j -> slot j & 1
         my_frames = sum(max(0, min(final_range(k, n_win)[1], n) - final_range(k, n_win)[0]) for k in mine)
-        out = alloc((max(1, my_frames) + INFER_LEN, fh, fw))      # this rank's final frames, in processing order
+        # this rank's final frames: all of them, in processing order, when they stay on the device; otherwise one window's
+        # worth that the stitch and its device->host copy (same stream) pass through
+        out = alloc(((max(1, my_frames) if return_device else 0) + INFER_LEN, fh, fw))
 
         # ---- where the result goes
         host = host_np = result = worker = jobs = None
@@ -360,8 +386,12 @@ class WindowedDepthDriver:
                 worker = threading.Thread(target=drain, daemon=True)
                 worker.start()
 
+        fwd_done = []   # per round: the event after its forward (None when the rank has no window in it)
+
         def upload(j):
             with torch.cuda.stream(up):
+                if j >= 2 and fwd_done[j - 2] is not None:
+                    up.wait_event(fwd_done[j - 2])   # group j % 3 was last read by windows j - 3 and j - 2
                 for (first, count, row0) in runs[j]:
                     self._upload_preprocess(frames, first, first + count, pre, nh, nw, row0=row0)
                 ev = torch.cuda.Event()
@@ -399,23 +429,26 @@ class WindowedDepthDriver:
                                                      fw, s), "vda_resize_depth")
                     m["f1"] = timed()
                     m["f1"].record(main)
+                    fwd_done.append(m["f1"])
                     side.wait_event(m["f1"])
                     if j + 1 < len(mine):
                         ev_up = upload(j + 1)
+                else:
+                    fwd_done.append(None)
                 with torch.cuda.stream(side):
                     m["x0"] = timed()
                     m["x0"].record(side)
                     stitcher.exchange(j)
                     m["x1"] = timed()
                     m["x1"].record(side)
-                    done = stitcher.round(j, raw[j & 1] if k is not None else None, out[pos:])
+                    done = stitcher.round(j, raw[j & 1] if k is not None else None, out[pos:] if return_device else out)
                     m["s1"] = timed()
                     m["s1"].record(side)
                     if done is not None and done[1] > 0:
                         lo, cnt = done
                         ranges.append((lo, cnt, pos))
                         if host is not None:
-                            host[lo:lo + cnt].copy_(out[pos:pos + cnt], non_blocking=True)
+                            host[lo:lo + cnt].copy_(out[:cnt], non_blocking=True)
                             if jobs is not None:
                                 landed = torch.cuda.Event()
                                 landed.record(side)

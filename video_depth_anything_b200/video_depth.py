@@ -116,9 +116,32 @@ class VideoDepthAnything(nn.Module):
                           "(wider exponent, 3 fewer mantissa bits) -- see INTEGRATION.md", RuntimeWarning, stacklevel=2)
         plan = self.plan(B, T, H, W, x.device, bf16, skip_tmp_block)
         depth = plan.run(x.to(torch.float32).flatten(0, 1))
+        self._fire_motion_module_hooks(plan, B, T, skip_tmp_block)
         # fp32 in both builds: under CUDA autocast the head's bilinear upsample is an fp32 op, so the output convs and
         # the result stay fp32; the identity resize + ReLU of video_depth.py:63-64 are numerical no-ops.
         return depth.clone().unflatten(0, (B, T))
+
+    def _fire_motion_module_hooks(self, plan, B, T, skip_tmp_block):
+        """Forward hooks registered on `model.head.motion_modules[i]` -- the reference's diagnostic harness grabs the temporal
+        modules' outputs that way (Test_singleImage_processing.py:132-142).  The modules here are parameter containers whose
+        `forward` never runs (the compute is a launch list), so the hooks are called by hand after the plan has run, with the
+        tensors the reference would pass: hook(module, (input [B,C,T,h,w], None, None), output [B,C,T,h,w]) as at
+        dpt_temporal.py:75-76,84-87 -- copies of the plan's buffers, in the build's activation type."""
+        mods = self.head.motion_modules
+        if not any(m._forward_hooks for m in mods):
+            return
+        ph, pw = plan.ph, plan.pw_
+        geo = [(ph, pw), ((ph + 1) // 2, (pw + 1) // 2), (ph, pw), (2 * ph, 2 * pw)]
+        names = [("layer_3", "mm0"), ("layer_4", "mm1"), ("path_4d", "path_4"), ("path_3d", "path_3")]
+        for i, m in enumerate(mods):
+            if not m._forward_hooks or (i == 2 and skip_tmp_block):
+                continue
+            h, w = geo[i]
+            xin = plan.bufs[names[i][0]].view(B, T, h, w, -1).permute(0, 4, 1, 2, 3).contiguous()
+            out = plan.bufs[names[i][1]].view(B, T, h + 2, w + 2, -1)[:, :, 1:-1, 1:-1].permute(0, 4, 1, 2, 3).contiguous()
+            for hook in list(m._forward_hooks.values()):
+                if hook(m, (xin, None, None), out) is not None:
+                    raise NotImplementedError("forward hooks on motion modules can observe the output but not replace it")
 
     # ------------------------------------------------------------------ streaming mode (video_depth.py:93-327)
     def infere_single_image(self, frames, target_fps, input_size=518, device="cuda", fp32=False, warmup=True,
