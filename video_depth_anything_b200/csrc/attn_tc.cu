@@ -213,11 +213,14 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         if (lane == 0) ptx::mbar_arrive(&bars[B_SFREE + sid]);  // the next S MMA of this stream may start
         FA_T(2);
         const int kvalid = ntok - j * BKV - hh * KH;  // keys >= kvalid (in this thread's 64) are outside the frame
-        if (kvalid < KH) {
+        if (kvalid < KH) {  // one select per packed pair, and one more pass only when the boundary splits a pair
+          const int inside = (kvalid + 1) >> 1;  // pairs with at least one key of the frame
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            if (2 * i >= kvalid) sp[i] = 0xFF80FF80u;
-            else if (2 * i + 1 >= kvalid) sp[i] = (sp[i] & 0xFFFFu) | 0xFF800000u;
+          for (int i = 0; i < 32; ++i) sp[i] = (i < inside) ? sp[i] : 0xFF80FF80u;
+          if (kvalid & 1) {
+            const int split = kvalid >> 1;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) sp[i] = (i == split) ? ((sp[i] & 0xFFFFu) | 0xFF800000u) : sp[i];
           }
         }
         uint32_t mxa = 0xFF80FF80u, mxb = 0xFF80FF80u;  // (-inf, -inf); two chains
