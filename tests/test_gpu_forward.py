@@ -307,6 +307,58 @@ def test_stream_contract():
         m.infere_single_image(frames[:20], 24, input_size=28, device="cuda", fp32=True, align_each_new_frame=False)
 
 
+@pytest.mark.parametrize("enc,T,H,W,pred,skip", [("vits", 8, 42, 56, None, False), ("vits", 6, 56, 42, [0, 3], False),
+                                                 ("vitl", 4, 28, 42, [1], True)])
+def test_tensor_level_single_image_entry_points(enc, T, H, W, pred, skip):
+    """`forward_single_image` (video_depth.py:67-91), `head.foward_single_image` (dpt_temporal.py:133-260) and
+    `head.get_motion_features` (:101-130) with caller-held context tensors, fp32 build against the oracle in strict fp32;
+    then the bf16 build under autocast against the oracle's autocast run through the usual gate."""
+    m, sd = get_model(enc)
+    ph, pw = H // 14, W // 14
+    frames = synthetic_clip(1, T, H, W, 23).to(dev)[0]   # T-1 context frames + the new one
+    old = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        with torch.no_grad():
+            taps_ctx = omodel.encoder_taps(sd, frames[:T - 1], enc)
+            feats_ref = omodel.reassemble(sd, taps_ctx, ph, pw)
+            x_new = frames[T - 1:].unsqueeze(0)
+            d_ref, new_ref = omodel.forward_single_image(sd, x_new, enc, tuple(feats_ref), None if pred is None else list(pred), T, skip)
+            taps_new = omodel.encoder_taps(sd, frames[T - 1:], enc)
+            # ---- get_motion_features: the context store from encoder features, (tokens, class token) pairs as the reference passes
+            feats = m.head.get_motion_features([(t, t[:, 0]) for t in taps_ctx], ph, pw)
+            for k in range(4):
+                assert feats[k].shape == feats_ref[k].shape
+                assert ((feats[k] - feats_ref[k]).abs().max() / feats_ref[k].abs().max()).item() <= 1e-4, k   # signed maps: to peak
+            # ---- model level
+            pred_arg = None if pred is None else list(pred)
+            d, new = m.forward_single_image(x_new, feats, pred_arg, inference_length=T, skip_tmp_block=skip)
+            assert pred_arg == (None if pred is None else list(pred))   # the reference appends and pops; the list comes back intact
+            n = 1 if pred is None else len(pred) + 1
+            assert d.shape == d_ref.shape == (1, n, H, W) and d.dtype == torch.float32
+            assert rel_err_map(d, d_ref).max().item() <= 1e-3
+            for k in range(4):
+                assert new[k].shape == new_ref[k].shape
+                assert ((new[k] - new_ref[k]).abs().max() / new_ref[k].abs().max()).item() <= 1e-4, k
+            # ---- head level, from the oracle's encoder features of the new frame
+            out = m.head.foward_single_image([(t, t[:, 0]) for t in taps_new], ph, pw, T, feats_ref, pred_arg, skip_tmp_block=skip)
+            assert len(out) == 5 and out[0].shape == (n, 1, H, W)
+            assert rel_err_map(out[0].squeeze(1), d_ref[0]).max().item() <= 1e-3
+            # ---- a context of the wrong length fails like the reference's unflatten
+            with pytest.raises(RuntimeError):
+                m.forward_single_image(x_new, tuple(f[:-1] for f in feats), None, inference_length=T)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        feats16 = omodel.reassemble(sd, omodel.encoder_taps(sd, frames[:T - 1], enc), ph, pw)
+        d16_ref, _ = omodel.forward_single_image(sd, x_new, enc, tuple(feats16), None if pred is None else list(pred), T, skip)
+        d16, new16 = m.forward_single_image(x_new, tuple(feats16), None if pred is None else list(pred), inference_length=T,
+                                            skip_tmp_block=skip)
+    assert new16[0].dtype == torch.bfloat16 and d16.dtype == torch.float32
+    bf16_gate(f"single_image_{enc}_T{T}", d16, d16_ref, d_ref)
+
+
 @pytest.mark.parametrize("enc,T,ph,pw", [("vits", 16, 5, 7), ("vits", 64, 4, 6), ("vitl", 16, 3, 4), ("vitl", 64, 2, 3)])
 def test_isolated_head_frames_16_64(enc, T, ph, pw):
     """BASELINE.json config 5: `DPTHeadTemporal.forward` alone on random taps, 16 and 64 frames (64 needs

@@ -696,7 +696,7 @@ class StreamPlan(ForwardPlan):
         super().__init__(pw, 1, T, H, W, device, skip_tmp_block, use_tc=use_tc, attn_tc=attn_tc)
 
     def _all_ops(self):
-        return [op for st in self.stages.values() for op in st["ops"]]
+        return [op for name, st in self.stages.items() if name != "reassemble" for op in st["ops"]]   # a slice of "encode"
 
     def _end_stage(self, name):
         self.stages[name] = {"ops": self.ops, "graph": None, "runs": 0}
@@ -721,9 +721,13 @@ class StreamPlan(ForwardPlan):
         # ---- encode: enc_batch frames into the incoming slots R .. R + enc_batch - 1
         self.BT, self._prefix = EB, "enc."
         self._alias = {f"layer_{k + 1}": self.rings[k][R:R + EB].reshape(EB * shapes[k][0], shapes[k][1]) for k in range(4)}
-        self._reassemble(self._build_encoder())
+        self.enc_taps = self._build_encoder()   # [EB * P, D] each: final norm applied, class token dropped
+        n_encoder_ops = len(self.ops)
+        self._reassemble(self.enc_taps)
         assert not self._alias
         self._end_stage("encode")
+        # the reassemble half on its own, for callers that bring their own encoder features (`foward_single_image`)
+        self.stages["reassemble"] = {"ops": self.stages["encode"]["ops"][n_encoder_ops:], "graph": None, "runs": 0}
 
         # ---- middle: the T-frame context (T-1 stored frames + the incoming one)
         self.BT, self._prefix = T, "mid."
@@ -767,6 +771,33 @@ class StreamPlan(ForwardPlan):
         self.BT, self._prefix = 1, ""
         self.depth = None
 
+    # ------------------------------------------------------------------ feature store <-> the reference's NCHW tensors
+    def ring_geometry(self):
+        """(h, w, padded) of layer_1..4: layers 1 and 2 are stored with a zero border (they feed 3x3 convs)."""
+        ph, pwid = self.ph, self.pw_
+        return [(4 * ph, 4 * pwid, True), (2 * ph, 2 * pwid, True), (ph, pwid, False), ((ph + 1) // 2, (pwid + 1) // 2, False)]
+
+    def store_features(self, k, slot0, t):
+        """Write t [n, C, h, w] (the reference's layout of layer_{k+1}, dpt_temporal.py:101-130) into ring slots slot0.."""
+        h, w, padded = self.ring_geometry()[k]
+        n, C_ = t.shape[0], self.rings[k].shape[2]
+        if tuple(t.shape[1:]) != (C_, h, w):
+            raise ValueError(f"layer_{k + 1}: expected [n, {C_}, {h}, {w}], got {list(t.shape)}")
+        src = t.to(device=self.device, dtype=self.adt).permute(0, 2, 3, 1)
+        dst = self.rings[k][slot0:slot0 + n]
+        if padded:
+            dst.view(n, h + 2, w + 2, C_)[:, 1:-1, 1:-1].copy_(src)
+        else:
+            dst.view(n, h, w, C_).copy_(src)
+
+    def load_features(self, k, slot):
+        """Ring slot -> [1, C, h, w] in the build's activation type."""
+        h, w, padded = self.ring_geometry()[k]
+        C_ = self.rings[k].shape[2]
+        v = self.rings[k][slot]
+        v = v.view(h + 2, w + 2, C_)[1:-1, 1:-1] if padded else v.view(h, w, C_)
+        return v.permute(2, 0, 1).unsqueeze(0).contiguous()
+
     # ------------------------------------------------------------------ execution
     def index_row(self, ctx=(), pred=(), p3=(), commit=(), src=()):
         """One step's index arrays as a host int32 [5, width] block (ring slots / context positions)."""
@@ -782,6 +813,7 @@ class StreamPlan(ForwardPlan):
         self.idx.copy_(row_dev, non_blocking=True)
 
     def run_stage(self, name):
+        """"encode" = encoder + reassemble; "reassemble" alone starts from `self.enc_taps` (written by the caller)."""
         st = self.stages[name]
         if st["graph"] is not None:
             st["graph"].replay()

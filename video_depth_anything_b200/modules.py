@@ -11,6 +11,7 @@ Key layout mirrored from the reference (file:line):
 from __future__ import annotations
 
 import math
+import weakref
 
 import torch
 import torch.nn as nn
@@ -196,3 +197,48 @@ class DPTHeadTemporalParams(nn.Module):
         self.motion_modules = nn.ModuleList(
             [TemporalModuleParams(c, num_frames, pe) for c in (oc[2], oc[3], features, features)]
         )
+
+    def _bind(self, owner):
+        """The compute lives in the owning model's launch plans; a weak reference keeps the module tree acyclic."""
+        object.__setattr__(self, "_owner", weakref.ref(owner))
+
+    def __getstate__(self):   # copy / pickle: the owner re-binds its head (VideoDepthAnything.__setstate__)
+        state = self.__dict__.copy()
+        state.pop("_owner", None)
+        return state
+
+    def _model(self):
+        owner = getattr(self, "_owner", None)
+        owner = owner() if owner is not None else None
+        if owner is None:
+            raise RuntimeError("this head is not attached to a VideoDepthAnything model")
+        return owner
+
+    def get_motion_features(self, out_features, patch_h, patch_w):
+        """projects + resize layers of n frames' encoder features (dpt_temporal.py:101-130): out_features = four
+        (patch tokens [n, P, D], class token) pairs as `get_intermediate_layers(..., return_class_token=True)` returns
+        them.  Returns layer_1..4, NCHW."""
+        model = self._model()
+        tok0 = out_features[0][0] if isinstance(out_features[0], (tuple, list)) else out_features[0]
+        n, dev = tok0.shape[0], tok0.device
+        bf16 = torch.is_autocast_enabled("cuda")
+        outs = [[] for _ in range(4)]
+        with torch.cuda.device(dev), torch.no_grad():
+            plan = model.stream_plan(1, 14 * patch_h, 14 * patch_w, dev, bf16, 1, (1,), False, enc_batch=1)
+            for i in range(n):
+                for tap, f in zip(plan.enc_taps, out_features):
+                    tok = f[0] if isinstance(f, (tuple, list)) else f
+                    tap.copy_(tok[i].reshape(patch_h * patch_w, -1))
+                plan.run_stage("reassemble")
+                for k in range(4):
+                    outs[k].append(plan.load_features(k, 1))
+        return tuple(torch.cat(o, 0) for o in outs)
+
+    def foward_single_image(self, out_features, patch_h, patch_w, frame_length, motion_features, pred_depth_idx=None,
+                            skip_tmp_block=False, max_head_pred_length=6):
+        """The head's streaming step (dpt_temporal.py:133-260; the reference spells it `foward`): the new frame's encoder
+        features + the stored layer_1..4 of the frame_length - 1 context frames -> (depth [n, 1, H, W], layer_1..4 of the
+        new frame).  `max_head_pred_length` only chunks the reference's per-frame tail to save memory; ignored."""
+        depth, feats = self._model()._single_image(None, out_features, patch_h, patch_w, frame_length, motion_features,
+                                                   pred_depth_idx, skip_tmp_block)
+        return (depth,) + tuple(feats)

@@ -45,6 +45,7 @@ class VideoDepthAnything(nn.Module):
         self.pe = pe
         self.pretrained = DinoV2Params(encoder)
         self.head = DPTHeadTemporalParams(self.pretrained.embed_dim, features, list(out_channels), num_frames, pe)
+        self.head._bind(self)
         self._packed = {}   # (device, bf16) -> (version key, PackedWeights)
         # (device, bf16, B, T, H, W, skip, ...) -> plan, least recently used first.  A plan owns every activation buffer of
         # its shape (vitl 518x518: ~20 GB), so the cache is capped: callers that walk over many resolutions (app.py,
@@ -54,6 +55,16 @@ class VideoDepthAnything(nn.Module):
         self._fp16_autocast_noted = False
         self.force_simt = False  # tests: run the bf16 build on the SIMT kernels instead of tcgen05
         self.attn_simt = False   # tests: tcgen05 GEMMs but the exact-rounding SIMT attention
+
+    def __getstate__(self):   # copy.deepcopy / torch.save(model): launch plans and packed weights are rebuilt on demand
+        state = self.__dict__.copy()
+        state["_packed"], state["_plans"] = {}, collections.OrderedDict()
+        state.pop("_last_driver", None)
+        return state
+
+    def __setstate__(self, state):
+        super().__setstate__(state)
+        self.head._bind(self)
 
     # ------------------------------------------------------------------ weights / plans
     def _weights_version(self):
@@ -142,6 +153,67 @@ class VideoDepthAnything(nn.Module):
             for hook in list(m._forward_hooks.values()):
                 if hook(m, (xin, None, None), out) is not None:
                     raise NotImplementedError("forward hooks on motion modules can observe the output but not replace it")
+
+    # ------------------------------------------------------------------ tensor-level streaming step (video_depth.py:67-91)
+    def forward_single_image(self, x, motion_features, pred_depth_idx=None, inference_length=32, skip_tmp_block=False):
+        """One new frame against caller-held context features: same arguments and return value as the reference.
+        x [1, 1, 3, H, W]; motion_features = (layer_1, layer_2, layer_3, layer_4) of the `inference_length - 1` context
+        frames, NCHW as `head.get_motion_features` / an earlier call returned them; pred_depth_idx: context rows that get
+        a depth map besides the new frame.  Returns (depth [1, n, H, W] fp32, (layer_1..4 of the new frame, [1, C, h, w])).
+
+        This is the reference's calling convention kept for callers that manage the store themselves: the four context
+        tensors are converted into the plan's channels-last store on every call.  `infere_single_image` keeps the store
+        on the device in that layout and is the fast path."""
+        B, T, _, H, W = x.shape
+        if B * T != 1:
+            raise ValueError(f"forward_single_image takes one frame [1, 1, 3, H, W], got {list(x.shape)}")
+        depth, feats = self._single_image(x, None, H // 14, W // 14, inference_length, motion_features, pred_depth_idx,
+                                          skip_tmp_block)
+        return depth.squeeze(1).unflatten(0, (B, depth.shape[0])), feats
+
+    def _single_image(self, x, out_features, patch_h, patch_w, frame_length, motion_features, pred_depth_idx, skip_tmp_block):
+        """Shared by `forward_single_image` (x given: the encoder runs) and `head.foward_single_image` (encoder features
+        given).  Returns (depth [n, 1, H, W] fp32, (layer_1..4 of the new frame))."""
+        ref = x if x is not None else out_features[0][0]
+        L.require_device(ref.device)
+        dev = ref.device
+        bf16 = torch.is_autocast_enabled("cuda")
+        T = int(frame_length)
+        H, W = 14 * patch_h, 14 * patch_w
+        if len(motion_features) != 4:
+            raise ValueError("motion_features must be (layer_1, layer_2, layer_3, layer_4)")
+        for k, t in enumerate(motion_features):
+            if t.shape[0] != T - 1:
+                # the reference fails in unflatten(0, (B, T)) when context + new frame is not exactly frame_length frames
+                raise RuntimeError(f"motion_features[{k}] holds {t.shape[0]} frames, frame_length - 1 = {T - 1} expected")
+        pred = [] if pred_depth_idx is None else [int(i) % (T - 1) if i < 0 else int(i) for i in pred_depth_idx]
+        if any(i >= T - 1 for i in pred):
+            raise IndexError(f"pred_depth_idx {pred_depth_idx} out of range for {T - 1} context frames")
+        n = len(pred) + 1
+        R = T - 1   # store rows 0..T-2 hold the context, slot R receives the new frame
+        with torch.cuda.device(dev), torch.no_grad():
+            plan = self.stream_plan(T, H, W, dev, bf16, R, (n,), skip_tmp_block, enc_batch=1)
+            for k, t in enumerate(motion_features):
+                plan.store_features(k, 0, t)
+            plan.load_indices(plan.index_row(ctx=list(range(T - 1)) + [R], pred=pred + [R], p3=pred + [T - 1]).to(dev))
+            if x is not None:
+                plan.x_in.copy_(x.reshape(1, 3, H, W).to(torch.float32))
+                plan.run_stage("encode")
+            else:
+                if len(out_features) != 4:
+                    raise ValueError("out_features must hold the four encoder taps")
+                P = patch_h * patch_w
+                for tap, f in zip(plan.enc_taps, out_features):
+                    tok = f[0] if isinstance(f, (tuple, list)) else f   # (patch tokens, class token), dinov2.py:309-321
+                    if tuple(tok.shape) != (1, P, tap.shape[1]):
+                        raise ValueError(f"encoder feature {list(tok.shape)}: expected [1, {P}, {tap.shape[1]}]")
+                    tap.copy_(tok.reshape(P, -1))
+                plan.run_stage("reassemble")
+            plan.run_stage("middle")
+            plan.run_stage(f"tail{n}")
+            depth = plan.depths[n].reshape(n, 1, H, W).clone()
+            feats = tuple(plan.load_features(k, R) for k in range(4))
+        return depth, feats
 
     # ------------------------------------------------------------------ streaming mode (video_depth.py:93-327)
     def infere_single_image(self, frames, target_fps, input_size=518, device="cuda", fp32=False, warmup=True,
