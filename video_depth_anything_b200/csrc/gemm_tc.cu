@@ -88,17 +88,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m0 = (tile / a.tiles_n) * BM, n0 = (tile % a.tiles_n) * BN;
+        // coordinates carried incrementally: this one thread feeds the TMA unit a k-block per 4 MMAs, no division per step
+        int kin = 0, tap = 0, bcol = 0;  // k-block inside the tap; tap; first B column of (split, tap) = st * K
+        int off = vda_tap_off(a.taps, 0, a.m_padded, a.gb, a.gh, a.gw);
         for (int kb = 0; kb < num_kb; ++kb) {
-          const int kin = kb % kb_per_tap, st = kb / kb_per_tap;  // st = s*taps + tap
-          const int tap = st % a.taps;
-          const int off = vda_tap_off(a.taps, tap, a.m_padded, a.gb, a.gh, a.gw);
           ptx::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
           uint8_t* sb = sa + C::A_BYTES;
           ptx::mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
           ptx::tma_load_2d(sa, &tmA, kin * BKE, m0 + off, &full[stage]);
-          ptx::tma_load_2d(sb, &tmB, st * a.K + kin * BKE, n0, &full[stage]);
+          ptx::tma_load_2d(sb, &tmB, bcol + kin * BKE, n0, &full[stage]);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+          if (++kin == kb_per_tap) {
+            kin = 0;
+            bcol += a.K;
+            if (++tap == a.taps) tap = 0;
+            off = vda_tap_off(a.taps, tap, a.m_padded, a.gb, a.gh, a.gw);
+          }
         }
       }
     }

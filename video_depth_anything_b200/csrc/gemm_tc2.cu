@@ -93,21 +93,30 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      // This one thread has to hand a k-block to the TMA unit every 512 clk (4 MMAs) for the tensor pipe to stay busy:
+      // the loop carries its coordinates incrementally (no division per k-block: k-block -> (split, tap, column) is a
+      // pair of counters) and keeps the leader's barrier address as one add.
+      const uint32_t lead_full0 = ptx::mapa(ptx::smem_u32(&full[0]), 0);
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         const int m0 = (tile / a.tiles_n) * (2 * BM) + (int)rank * BM;
         const int n0 = (tile % a.tiles_n) * BN + (int)rank * (BN / 2);
+        int kin = 0, tap = 0, bcol = 0;  // k-block inside the tap; tap; first B column of (split, tap) = st * K
+        int off = vda_tap_off(a.taps, 0, a.m_padded, a.gb, a.gh, a.gw);
         for (int kb = 0; kb < num_kb; ++kb) {
-          const int kin = kb % kb_per_tap, st = kb / kb_per_tap;  // st = s*taps + tap
-          const int tap = st % a.taps;
-          const int off = vda_tap_off(a.taps, tap, a.m_padded, a.gb, a.gh, a.gw);
           ptx::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
-          const uint32_t lead_full = ptx::mapa(ptx::smem_u32(&full[stage]), 0);
+          const uint32_t lead_full = lead_full0 + stage * 8;
           if (rank == 0) ptx::mbar_arrive_expect_tx(&full[stage], 2 * STAGE_BYTES);
           ptx::tma_load_2d_pair(sa, &tmA, kin * BK, m0 + off, lead_full);
-          ptx::tma_load_2d_pair(sb, &tmB, st * a.K + kin * BK, n0, lead_full);
+          ptx::tma_load_2d_pair(sb, &tmB, bcol + kin * BK, n0, lead_full);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (++kin == kb_per_tap) {
+            kin = 0;
+            bcol += a.K;
+            if (++tap == a.taps) tap = 0;
+            off = vda_tap_off(a.taps, tap, a.m_padded, a.gb, a.gh, a.gw);
+          }
         }
       }
     }
