@@ -8,6 +8,8 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from video_depth_anything_b200 import lib as L  # noqa: E402
 
+if os.environ.get("VDA_LIB"):   # A/B against an experimental build of the library
+    L.LIB_PATH = os.environ["VDA_LIB"]
 dev = "cuda"
 L.require_device(dev)
 M = 43840
@@ -25,7 +27,7 @@ for N, K in [(1024, 1024), (1024, 4096), (1024, 16384), (2048, 8192), (4096, 102
         L.gemm(d)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n = 10
+    n = 30
     e0.record()
     for _ in range(n):
         L.gemm(d)

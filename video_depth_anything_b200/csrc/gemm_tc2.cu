@@ -54,7 +54,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* tempty = bars + 2 * STAGES + 2; // [2]       epilogue (both CTAs) -> MMA; only the leader's are used
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = (int)ptx::uniform_u32(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();  // 0 = leader
   const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
   const int kb_per_tap = (a.K + BK - 1) / BK;
@@ -86,11 +86,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   __syncthreads();
   ptx::cluster_sync();  // the peer's barriers are initialised before anything signals them
   ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = ptx::uniform_u32(*tmem_slot);
 
   if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer (both CTAs)
-    if (lane == 0) {
+    // ------------------------------------------------------------------ TMA producer (both CTAs): the warp walks the loop,
+    // one elected lane issues
+    {
       int stage = 0;
       uint32_t phase = 0;
       // This one thread has to hand a k-block to the TMA unit every 512 clk (4 MMAs) for the tensor pipe to stay busy:
@@ -107,9 +108,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
           const uint32_t lead_full = lead_full0 + stage * 8;
-          if (rank == 0) ptx::mbar_arrive_expect_tx(&full[stage], 2 * STAGE_BYTES);
-          ptx::tma_load_2d_pair(sa, &tmA, kin * BK, m0 + off, lead_full);
-          ptx::tma_load_2d_pair(sb, &tmB, bcol + kin * BK, n0, lead_full);
+          if (ptx::elect_one()) {
+            if (rank == 0) ptx::mbar_arrive_expect_tx(&full[stage], 2 * STAGE_BYTES);
+            ptx::tma_load_2d_pair(sa, &tmA, kin * BK, m0 + off, lead_full);
+            ptx::tma_load_2d_pair(sb, &tmB, bcol + kin * BK, n0, lead_full);
+          }
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
           if (++kin == kb_per_tap) {
             kin = 0;
@@ -121,8 +125,9 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (leader CTA only)
-    if (lane == 0 && rank == 0) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA only): warp-uniform loop,
+    // one elected lane issues
+    if (rank == 0) {
       constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * BM, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
@@ -139,11 +144,14 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint32_t sb = sa + A_BYTES;
           const uint64_t da = ptx::make_sw128_desc(sa, 16, 1024);
           const uint64_t db = ptx::make_sw128_desc(sb, 16, 1024);
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            ptx::mma_f16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-          ptx::tc_commit_pair(&empty[stage], 3);
-          if (kb == num_kb - 1) ptx::tc_commit_pair(&tfull[acc], 3);
+            for (int k = 0; k < BK / 16; ++k)
+              ptx::mma_f16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            ptx::tc_commit_pair(&empty[stage], 3);
+            if (kb == num_kb - 1) ptx::tc_commit_pair(&tfull[acc], 3);
+          }
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }

@@ -43,6 +43,21 @@ __device__ __forceinline__ uint32_t mbar_test(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok;
 }
+// One lane of a converged warp.  Role loops that are executed by the WHOLE warp with the issuing instructions under this
+// predicate keep their operands warp-uniform for the compiler (uniform registers feed UTMALDG / UTCHMMA directly); a loop
+// under `if (lane == 0)` is divergent code whose every TMA / MMA operand goes through an ELECT + R2UR.BROADCAST waterfall.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// A value the compiler may treat as warp-uniform (lane 0's copy).
+__device__ __forceinline__ uint32_t uniform_u32(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   long long t0 = clock64();
