@@ -87,7 +87,7 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + NBARS);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = (int)ptx::uniform_u32(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * BQ, h = blockIdx.y, f = blockIdx.z;
   const int D = heads * HD;
   const int nblk = (ntok + BKV - 1) / BKV;
@@ -122,28 +122,40 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
+  const uint32_t tmem = ptx::uniform_u32(*tmem_slot);
 
   if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      ptx::mbar_arrive_expect_tx(&bars[B_QFULL], TILE_BYTES);
-      ptx::tma_load_2d(smem + OFF_Q, &tm, h * HD, row0 + q0, &bars[B_QFULL]);
+    // ------------------------------------------------------------------ TMA producer.  This loop and the MMA issuers'
+    // are walked by the whole warp, the issuing instructions sit under ptx::elect_one(): the operands stay in uniform
+    // registers instead of going through an ELECT + R2UR waterfall per instruction (ptx.cuh) -- here that latency sits
+    // on the softmax warps' dependent chain.
+    {
+      if (ptx::elect_one()) {
+        ptx::mbar_arrive_expect_tx(&bars[B_QFULL], TILE_BYTES);
+        ptx::tma_load_2d(smem + OFF_Q, &tm, h * HD, row0 + q0, &bars[B_QFULL]);
+      }
+      __syncwarp();
       for (int j = 0; j < nblk; ++j) {
         const int s = j % NS;
         const uint32_t ph = (j / NS) & 1;
         ptx::mbar_wait(&bars[B_KEMPTY + s], ph ^ 1);
-        ptx::mbar_arrive_expect_tx(&bars[B_KFULL + s], TILE_BYTES);
-        ptx::tma_load_2d(smem + OFF_K + s * TILE_BYTES, &tm, D + h * HD, row0 + j * BKV, &bars[B_KFULL + s]);
+        if (ptx::elect_one()) {
+          ptx::mbar_arrive_expect_tx(&bars[B_KFULL + s], TILE_BYTES);
+          ptx::tma_load_2d(smem + OFF_K + s * TILE_BYTES, &tm, D + h * HD, row0 + j * BKV, &bars[B_KFULL + s]);
+        }
+        __syncwarp();
         ptx::mbar_wait(&bars[B_VEMPTY + s], ph ^ 1);
-        ptx::mbar_arrive_expect_tx(&bars[B_VFULL + s], TILE_BYTES);
-        ptx::tma_load_2d(smem + OFF_V + s * TILE_BYTES, &tm, 2 * D + h * HD, row0 + j * BKV, &bars[B_VFULL + s]);
+        if (ptx::elect_one()) {
+          ptx::mbar_arrive_expect_tx(&bars[B_VFULL + s], TILE_BYTES);
+          ptx::tma_load_2d(smem + OFF_V + s * TILE_BYTES, &tm, 2 * D + h * HD, row0 + j * BKV, &bars[B_VFULL + s]);
+        }
+        __syncwarp();
       }
     }
   } else if (warp <= NSTREAM) {
     // ------------------------------------------------------------------ MMA issuer of stream warp-1
     const int sid = warp - 1, hh = sid;
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc_s = ptx::make_idesc_bf16(BQ, KH, 0, 0);
       constexpr uint32_t idesc_pv = ptx::make_idesc_bf16(BQ, HD, 0, 1);  // B = V is MN-major (d contiguous)
       const uint64_t dq = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_Q), 16, 1024);
@@ -155,11 +167,14 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         if (j > 0) ptx::mbar_wait(&bars[B_SFREE + sid], (j - 1) & 1);  // the softmax warps hold S(j-1) in registers
         ptx::tc_fence_after();
         const uint64_t dk = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_K + s * TILE_BYTES + hh * (KH * 128)), 16, 1024);
+        if (ptx::elect_one()) {
 #pragma unroll
-        for (int k = 0; k < HD / 16; ++k) ptx::mma_f16_ss(ds_tmem, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
-        ptx::tc_commit(&bars[B_SFULL + sid]);
-        ptx::tc_commit(&bars[B_KEMPTY + s]);
-        if (j == nblk - 1) ptx::tc_commit(&bars[B_QFREE]);
+          for (int k = 0; k < HD / 16; ++k) ptx::mma_f16_ss(ds_tmem, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+          ptx::tc_commit(&bars[B_SFULL + sid]);
+          ptx::tc_commit(&bars[B_KEMPTY + s]);
+          if (j == nblk - 1) ptx::tc_commit(&bars[B_QFREE]);
+        }
+        __syncwarp();
       };
       ptx::mbar_wait(&bars[B_QFULL], 0);
       issue_s(0);
@@ -170,13 +185,16 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         ptx::mbar_wait(&bars[B_PFULL + sid], j & 1);  // P(j) is in smem, PV(j-1) has been read out of TMEM if rescaled
         ptx::tc_fence_after();
         const uint32_t sv = ptx::smem_u32(smem + OFF_V + s * TILE_BYTES) + hh * (KH * 128);
+        if (ptx::elect_one()) {
 #pragma unroll
-        for (int k = 0; k < KH / 16; ++k) {
-          const uint64_t dv = ptx::make_sw128_desc(sv + k * 2048, 1024, 1024);
-          ptx::mma_f16_ss(do_tmem, dp + 2 * k, dv, idesc_pv, (j | k) != 0);  // O accumulates in TMEM
+          for (int k = 0; k < KH / 16; ++k) {
+            const uint64_t dv = ptx::make_sw128_desc(sv + k * 2048, 1024, 1024);
+            ptx::mma_f16_ss(do_tmem, dp + 2 * k, dv, idesc_pv, (j | k) != 0);  // O accumulates in TMEM
+          }
+          ptx::tc_commit(&bars[B_PVDONE + sid]);
+          ptx::tc_commit(&bars[B_VEMPTY + s]);
         }
-        ptx::tc_commit(&bars[B_PVDONE + sid]);
-        ptx::tc_commit(&bars[B_VEMPTY + s]);
+        __syncwarp();
       }
     }
   } else {

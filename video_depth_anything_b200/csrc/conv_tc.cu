@@ -58,7 +58,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
   static_assert((2 * NA + 2 * NB + 4) * 8 + 8 <= 256, "barrier area");
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = (int)ptx::uniform_u32(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int kchunks = a.K / BK;
   const int ngroups = 3 * kchunks;  // (k-block, dy)
   const int num_tiles = a.tiles_m * a.tiles_n;
@@ -82,11 +82,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = ptx::uniform_u32(*tmem_slot);
 
+  // role loops walked by the whole warp, issuing instructions under ptx::elect_one() (uniform-register operands, ptx.cuh)
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    {
       int as = 0, bs = 0;
       uint32_t aph = 0, bph = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -94,16 +95,22 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int g = 0; g < ngroups; ++g) {
           const int kc = g / 3, dy = g % 3;
           ptx::mbar_wait(&aempty[as], aph ^ 1);
-          ptx::mbar_arrive_expect_tx(&afull[as], A_BYTES);
           uint8_t* sa = smem + as * A_BYTES;
           const int r0 = m0 + (dy - 1) * a.W2 - 1;  // rows before / past the map are zero-filled by TMA
+          if (ptx::elect_one()) {
+            ptx::mbar_arrive_expect_tx(&afull[as], A_BYTES);
 #pragma unroll
-          for (int i = 0; i < 3; ++i) ptx::tma_load_2d(sa + i * A_BOX_BYTES, &tmA, kc * BK, r0 + i * A_BOX_ROWS, &afull[as]);
+            for (int i = 0; i < 3; ++i) ptx::tma_load_2d(sa + i * A_BOX_BYTES, &tmA, kc * BK, r0 + i * A_BOX_ROWS, &afull[as]);
+          }
+          __syncwarp();
           if (++as == NA) { as = 0; aph ^= 1; }
           for (int dx = 0; dx < 3; ++dx) {
             ptx::mbar_wait(&bempty[bs], bph ^ 1);
-            ptx::mbar_arrive_expect_tx(&bfull[bs], B_BYTES);
-            ptx::tma_load_2d(smem + OFF_B + bs * B_BYTES, &tmB, (dy * 3 + dx) * a.K + kc * BK, n0, &bfull[bs]);
+            if (ptx::elect_one()) {
+              ptx::mbar_arrive_expect_tx(&bfull[bs], B_BYTES);
+              ptx::tma_load_2d(smem + OFF_B + bs * B_BYTES, &tmB, (dy * 3 + dx) * a.K + kc * BK, n0, &bfull[bs]);
+            }
+            __syncwarp();
             if (++bs == NB) { bs = 0; bph ^= 1; }
           }
         }
@@ -111,7 +118,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = ptx::make_idesc_bf16(BM, BN, 0, 0);
       int as = 0, bs = 0, acc = 0;
       uint32_t aph = 0, bph = 0, acc_phase = 0;
@@ -125,21 +132,26 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             ptx::mbar_wait(&bfull[bs], bph);
             ptx::tc_fence_after();
             const uint64_t db = ptx::make_sw128_desc(ptx::smem_u32(smem + OFF_B + bs * B_BYTES), 16, 1024);
+            if (ptx::elect_one()) {
 #pragma unroll
-            for (int i = 0; i < 2; ++i) {
-              // rows [128 i + dx, +128) of the 264-row A slot: the start address moves by whole 128 B rows
-              const uint64_t da = ptx::make_sw128_desc(sa + (i * BM + dx) * 128, 16, 1024);
-              const uint32_t d_tmem = tmem_base + (acc * 2 + i) * BN;
+              for (int i = 0; i < 2; ++i) {
+                // rows [128 i + dx, +128) of the 264-row A slot: the start address moves by whole 128 B rows
+                const uint64_t da = ptx::make_sw128_desc(sa + (i * BM + dx) * 128, 16, 1024);
+                const uint32_t d_tmem = tmem_base + (acc * 2 + i) * BN;
 #pragma unroll
-              for (int k = 0; k < BK / 16; ++k) ptx::mma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (g | dx | k) != 0);
+                for (int k = 0; k < BK / 16; ++k) ptx::mma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (g | dx | k) != 0);
+              }
+              ptx::tc_commit(&bempty[bs]);
+              if (dx == 2) {
+                ptx::tc_commit(&aempty[as]);
+                if (g == ngroups - 1) ptx::tc_commit(&tfull[acc]);
+              }
             }
-            ptx::tc_commit(&bempty[bs]);
+            __syncwarp();
             if (++bs == NB) { bs = 0; bph ^= 1; }
           }
-          ptx::tc_commit(&aempty[as]);
           if (++as == NA) { as = 0; aph ^= 1; }
         }
-        ptx::tc_commit(&tfull[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }

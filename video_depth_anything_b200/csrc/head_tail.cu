@@ -97,7 +97,7 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + HT_NBARS);
   float* spar = reinterpret_cast<float*>(smem + OFF_PAR);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = (int)ptx::uniform_u32(threadIdx.x >> 5), lane = threadIdx.x & 31;
   constexpr int KC = H ? 64 : 32;  // channels per chunk
   // grid-uniform early outs of the guarded form (the flag was written by an earlier kernel on this stream)
   if (a.skip_if_set != nullptr && *a.skip_if_set != 0) return;
@@ -131,7 +131,7 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = ptx::uniform_u32(*tmem_slot);
   const int tiles_per_frame = a.tiles_x * a.tiles_y;
 
   if (warp < NPROD_WARPS) {
@@ -242,22 +242,27 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
       }
     }
   } else if (warp == NPROD_WARPS) {
-    // ------------------------------------------------------------------ weight loader (TMA)
-    if (lane == 0) {
+    // ------------------------------------------------------------------ weight loader (TMA); the warp walks the loop, an
+    // elected lane issues (operands stay in uniform registers, ptx.cuh)
+    {
       uint32_t bcnt = 0;
       for (int g = blockIdx.x; g < a.ngroups; g += gridDim.x) {
         for (int kc = 0; kc < a.nkc; ++kc, ++bcnt) {
           const int bb = bcnt % NBBUF;
           ptx::mbar_wait(&bars[BB_EMPTY + bb], ((bcnt / NBBUF) & 1) ^ 1);
-          ptx::mbar_arrive_expect_tx(&bars[BB_FULL + bb], BBUF);
-          for (int tap = 0; tap < 9; ++tap)
-            ptx::tma_load_2d(smem + OFF_B + bb * BBUF + tap * 4096, &tmW, tap * a.C + kc * KC, 0, &bars[BB_FULL + bb]);
+          if (ptx::elect_one()) {
+            ptx::mbar_arrive_expect_tx(&bars[BB_FULL + bb], BBUF);
+            for (int tap = 0; tap < 9; ++tap)
+              ptx::tma_load_2d(smem + OFF_B + bb * BBUF + tap * 4096, &tmW, tap * a.C + kc * KC, 0, &bars[BB_FULL + bb]);
+          }
+          __syncwarp();
         }
       }
     }
   } else if (warp == NPROD_WARPS + 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // ------------------------------------------------------------------ MMA issuer (warp-uniform loop, elected lane issues:
+    // these MMAs are short -- N = 32 -- so the kernel lives off the issue rate of this one warp)
+    {
       constexpr uint32_t idesc = H ? ptx::make_idesc_f16(128, NOUT) : ptx::make_idesc_tf32(128, NOUT);
       uint32_t acnt = 0, bcnt = 0, gcnt = 0;
       for (int g = blockIdx.x; g < a.ngroups; g += gridDim.x, ++gcnt) {
@@ -275,22 +280,27 @@ head_tail_kernel(const __grid_constant__ CUtensorMap tmW, const HtArgs a) {
             ptx::tc_fence_after();
             const uint32_t sa = ptx::smem_u32(smem + OFF_A + ab * ABUF);
             const uint32_t d_tmem = tmem_base + gb * (GROUP * NOUT) + t * NOUT;
+            if (ptx::elect_one()) {
 #pragma unroll
-            for (int tap = 0; tap < 9; ++tap) {
-              const uint32_t a0 = sa + ((tap / 3) * PW + (tap % 3)) * 16;  // halo pixel (1+dy, 1+dx), dy,dx = tap/3-1, tap%3-1
-              const uint64_t db = ptx::make_sw128_desc(sb + tap * 4096, 16, 1024);
+              for (int tap = 0; tap < 9; ++tap) {
+                const uint32_t a0 = sa + ((tap / 3) * PW + (tap % 3)) * 16;  // halo pixel (1+dy, 1+dx), dy,dx = tap/3-1, tap%3-1
+                const uint64_t db = ptx::make_sw128_desc(sb + tap * 4096, 16, 1024);
 #pragma unroll
-              for (int kk = 0; kk < NSLAB / 2; ++kk) {  // one MMA covers two slabs (K = 8 fp32 or 16 fp16) = 32 B of a weight row
-                const uint64_t da = make_noswz_desc(a0 + (2 * kk) * SLAB, SLAB, PW * 16);
-                if (H) ptx::mma_f16_ss(d_tmem, da, db + 2 * kk, idesc, (kc | tap | kk) != 0);
-                else ptx::mma_tf32_ss(d_tmem, da, db + 2 * kk, idesc, (kc | tap | kk) != 0);
+                for (int kk = 0; kk < NSLAB / 2; ++kk) {  // one MMA covers two slabs (K = 8 fp32 or 16 fp16) = 32 B of a weight row
+                  const uint64_t da = make_noswz_desc(a0 + (2 * kk) * SLAB, SLAB, PW * 16);
+                  if (H) ptx::mma_f16_ss(d_tmem, da, db + 2 * kk, idesc, (kc | tap | kk) != 0);
+                  else ptx::mma_tf32_ss(d_tmem, da, db + 2 * kk, idesc, (kc | tap | kk) != 0);
+                }
+              }
+              ptx::tc_commit(&bars[BA_EMPTY + ab]);
+              if (t == nt - 1) {
+                ptx::tc_commit(&bars[BB_EMPTY + bb]);
+                if (kc == a.nkc - 1) ptx::tc_commit(&bars[BACC_FULL + gb]);
               }
             }
-            ptx::tc_commit(&bars[BA_EMPTY + ab]);
+            __syncwarp();
           }
-          ptx::tc_commit(&bars[BB_EMPTY + bb]);
         }
-        ptx::tc_commit(&bars[BACC_FULL + gb]);
       }
     }
   } else {
