@@ -9,6 +9,8 @@ import torch
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), ".."))
 from video_depth_anything_b200 import lib as L  # noqa: E402
 
+if os.environ.get("VDA_LIB"):
+    L.LIB_PATH = os.environ["VDA_LIB"]
 lib = L.load()
 dev = torch.device("cuda:0")
 frames, ntok, heads = 32, 1370, 16
