@@ -8,6 +8,8 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from video_depth_anything_b200 import lib as L  # noqa: E402
 
+if os.environ.get("VDA_LIB"):   # A/B against an experimental build of the library
+    L.LIB_PATH = os.environ["VDA_LIB"]
 dev = "cuda"
 L.require_device(dev)
 lib = L.load()
@@ -50,11 +52,23 @@ for name, N, K, kind in shapes:
         L.gemm(d)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n = 20
+    n = int(os.environ.get("GEMM_BENCH_ITERS", "20"))
     e0.record()
     for _ in range(n):
         L.gemm(d)
     e1.record()
+    clk = pw = ""
+    if n >= 200:  # long enough to sample the SM clock and board power under load (the step runs at the power cap)
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(0)
+        cs, ps = [], []
+        while not e1.query():
+            cs.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+            ps.append(pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0)
+        if cs:
+            cs, ps = sorted(cs[len(cs) // 3:]), sorted(ps[len(ps) // 3:])
+            clk, pw = f"  sm {cs[len(cs) // 2]} MHz", f"  {ps[len(ps) // 2]:.0f} W"
     torch.cuda.synchronize()
     us = e0.elapsed_time(e1) * 1e3 / n
-    print(f"{name:5s} M={M} N={N} K={K} {kind:6s}: {us:8.1f} us  {2.0 * M * N * K / us / 1e6:8.1f} TFLOP/s  (VDA_NO_PAIR={os.environ.get('VDA_NO_PAIR', '0')})")
+    print(f"{name:5s} M={M} N={N} K={K} {kind:6s}: {us:8.1f} us  {2.0 * M * N * K / us / 1e6:8.1f} TFLOP/s{clk}{pw}  (VDA_NO_PAIR={os.environ.get('VDA_NO_PAIR', '0')})")

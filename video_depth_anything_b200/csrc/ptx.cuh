@@ -92,8 +92,12 @@ __device__ __forceinline__ uint32_t mapa(uint32_t smem_addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
   return r;
 }
+// Arrive on a barrier of (possibly) the peer CTA, RELAXED: a release at cluster scope compiles to MEMBAR.ALL + ERRBAR, i.e.
+// the warp sits until every global store it has in flight is acknowledged (17 % of the pair GEMM's stall samples with the
+// epilogue's output stores pending).  What the waiter needs ordered here are this warp's TMEM reads, and those are
+// complete (tcgen05.wait::ld, then fence::before_thread_sync) before the arrive is issued.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load issued by either CTA of a pair; the completion bytes are signalled on `bar_cluster_addr`, which may live in
 // the peer CTA (the pair's leader waits for both halves of a stage on its own barrier).
