@@ -393,7 +393,31 @@ def clip_forward_bench(model, enc, size, device, steps, warmup, rank, local_rank
                          "share_of_step": gemm_ms / ms_total}}
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """The driver reads ONE JSON line from stdout.  Libraries write there too (NCCL prints its version banner on stdout whenever
+    NCCL_DEBUG is set, whatever NCCL_DEBUG_FILE says), so the process's fd 1 is pointed at stderr for everybody else and the
+    JSON line goes to the saved descriptor."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -445,7 +469,7 @@ def main():
         line = dict(base, impl="reference", value=fps, ms_per_step=dt * 1e3, dtype="f32", warmup=w, config=config,
                     cpu_baseline=dict({"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample}, **extra),
                     e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, gpu_launches=0)
-        print(json.dumps(line))
+        emit(line)
         return
 
     from video_depth_anything_b200 import lib as L
@@ -456,8 +480,6 @@ def main():
     dist = group = None
     if world > 1:
         import torch.distributed as dist
-        # NCCL prints its version banner on stdout when NCCL_DEBUG is set in the environment: keep stdout to the one JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=device)
         group = dist.group.WORLD
     model = build_model(enc, device)
@@ -495,7 +517,7 @@ def main():
             line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": f"oracle (CPU restatement of the reference forward) on {a.cpu_sample_frames} of the clip's "
                                               f"{T} frames (1x{a.cpu_sample_frames}x3x{size}x{size}), fp32, {os.cpu_count()} threads, {dt:.1f} s"}
-        print(json.dumps(line))
+        emit(line)
         return
 
     # ------------------------------------------------------------------ N > 1: the window-sharded long video (configs[3])
@@ -543,7 +565,7 @@ def main():
                     clip_forward={"value": clip["value"], "ms_per_step": clip["ms_per_step"], "e2e": clip["e2e"],
                                   "what": "the N = 1 workload (vitl 1x32x518x518 forward) on every rank at once: replicas, no exchange"},
                     env_toggles=toggles)
-        print(json.dumps(line))
+        emit(line)
     dist.barrier(group)
     dist.destroy_process_group()
 
