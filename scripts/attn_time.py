@@ -12,7 +12,8 @@ if os.environ.get("VDA_LIB"):
     L.LIB_PATH = os.environ["VDA_LIB"]
 lib = L.load()
 dev = torch.device("cuda:0")
-frames, ntok, heads = 32, 1370, 16
+frames, heads = 32, 16
+ntok = int(sys.argv[1]) if len(sys.argv) > 1 else 1370   # 2443 = the 518x924 network input of configs[3]
 qkv = (torch.randn(frames * ntok, 3 * heads * 64, device=dev) * 1.3).bfloat16()
 o = torch.empty(frames * ntok, heads * 64, device=dev, dtype=torch.bfloat16)
 f = lambda: L.check(lib.vda_attention(qkv.data_ptr(), o.data_ptr(), L.BF16, frames, ntok, heads, 1, 1, L.stream_ptr()), "attn")  # noqa: E731
@@ -25,4 +26,4 @@ for _ in range(20):
     f()
 e1.record()
 torch.cuda.synchronize()
-print("attention %.1f us  (%s)" % (e0.elapsed_time(e1) * 50, os.environ.get("VDA_LIB", "in-tree library")))
+print("attention ntok=%d %.1f us  (%s)" % (ntok, e0.elapsed_time(e1) * 50, os.environ.get("VDA_LIB", "in-tree library")))
