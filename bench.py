@@ -549,6 +549,12 @@ def main():
         n_win = config["windows_per_step"]
         st0 = stages_all[0] or {}
         launches = (clip["launches_per_window"] + 12 + 3 * world) * n_win * a.steps
+        # BASELINE.json's metric is clips at 1 GPU and long videos at 2 / 4 / 8: the N = 1 line times configs[1], this line
+        # configs[3], so v_N / (N v_1) across the two lines compares different workloads (a 518x924 window costs 2.1x a
+        # 518x518 clip).  The single-GPU figure for THIS video, measured in this run, is single_gpu_same_workload.
+        config = dict(config, n1_line_workload="configs[1] (one 32-frame 518x518 clip forward); same-video single-GPU run: "
+                                                 "single_gpu_same_workload", replicated_clip_forward="clip_forward (the N = 1 "
+                                                 "workload on every rank at once)")
         line = dict(base, value=r["device"]["value"], ms_per_step=r["device"]["s_per_pass"] * 1e3, dtype="bf16", config=config,
                     clocks=clocks,
                     e2e={"value": r["e2e"]["value"], "unit": "frames/s", "h2d_bytes_per_step": r["e2e"]["h2d_bytes_per_pass"],
