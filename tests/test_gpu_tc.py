@@ -281,3 +281,53 @@ def test_output_head_guarded_falls_back_to_tf32_outside_fp16_range(Ci, ih, iw, o
     # back in range: the flag is cleared by the call itself
     (g, h, t), ref, fl = run(x)
     assert fl == 0 and torch.equal(g, h)
+
+
+@pytest.mark.parametrize("kind", ["store", "gelu", "resid"])
+def test_pair_gemm_is_bit_reproducible_back_to_back(kind):
+    """The pipeline hand-offs of the pair GEMM (relaxed cluster arrive on the accumulator-free barrier, elected-lane issue,
+    double-buffered TMEM accumulators) carry no data: a hand-off that fired early would let an MMA overwrite an accumulator
+    that is still being read, which shows as outputs that change from launch to launch.  40 back-to-back launches on an
+    encoder-sized problem (27 tiles per CTA pair) must reproduce the first launch bit for bit."""
+    L, lib = _lib()
+    torch.manual_seed(5)
+    M, N, K = 43840, 1024, 1024
+    A = torch.randn(M, K, device=dev).bfloat16()
+    B = (torch.randn(N, K, device=dev) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device=dev)
+    base = dict(A=A, B=B, lda=K, ldb=K, rowsA=M, a_dtype=L.BF16, b_dtype=L.BF16, M=M, N=N, K=K, taps=1, ksplit=1, bias=bias,
+                round_bf16=1, out_dtype=L.BF16, use_tc=1)
+    gam = torch.rand(N, device=dev) + 0.5
+    first = None
+    for it in range(40):
+        if kind == "resid":
+            out = torch.zeros(M, N, device=dev)   # resid += gamma * R(acc + bias): one reduction per element and launch
+            run_gemm(L, lib, resid=out, gamma=gam, ldresid=N, **base)
+        else:
+            out = torch.full((M, N), float("nan"), device=dev, dtype=torch.bfloat16)
+            run_gemm(L, lib, out=out, ldo=N, act=L.ACT_GELU if kind == "gelu" else L.ACT_NONE, **base)
+        if first is None:
+            first = out
+            ref = A[:512].float() @ B.float().T + bias
+            if kind == "gelu":
+                ref = F.gelu(R(ref))
+            got = out[:512].float() / gam if kind == "resid" else out[:512].float()
+            assert (got - ref).abs().max().item() < 0.05 * ref.abs().max().item()
+        else:
+            assert torch.equal(out, first), (kind, it)
+
+
+def test_flash_attention_is_bit_reproducible_back_to_back():
+    L, lib = _lib()
+    torch.manual_seed(6)
+    frames, ntok, heads = 32, 1370, 16
+    qkv = (torch.randn(frames * ntok, 3 * heads * 64, device=dev) * 1.3).bfloat16()
+    first = None
+    for it in range(20):
+        o = torch.full((frames * ntok, heads * 64), float("nan"), device=dev, dtype=torch.bfloat16)
+        L.check(lib.vda_attention(qkv.data_ptr(), o.data_ptr(), L.BF16, frames, ntok, heads, 1, 1, L.stream_ptr()), "attn_tc")
+        if first is None:
+            first = o
+            assert torch.isfinite(o.float()).all()
+        else:
+            assert torch.equal(o, first), it
