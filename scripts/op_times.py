@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--encoder", default="vitl")
     ap.add_argument("--frames", type=int, default=32)
     ap.add_argument("--size", type=int, default=518)
+    ap.add_argument("--width", type=int, default=0, help="network width if not square (924 = configs[3]'s 518x924)")
     ap.add_argument("--repeats", type=int, default=7)
     ap.add_argument("--out", default="gpurun_out/op_times.json")
     ap.add_argument("--in-situ", action="store_true", help="time the ops inside back-to-back steps (events between ops, no flush)")
@@ -28,7 +29,7 @@ def main():
     torch.manual_seed(0)
     model = build_model(a.encoder, dev)  # the shipped configuration of that encoder (features, out_channels)
     pw = PackedWeights(model, dev, bf16=True)
-    plan = ForwardPlan(pw, 1, a.frames, a.size, a.size, dev)
+    plan = ForwardPlan(pw, 1, a.frames, a.size, a.width or a.size, dev)
     plan.x_in.normal_()
     lib = plan._lib
     st = L.stream_ptr()
