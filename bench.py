@@ -89,7 +89,7 @@ class ClockSampler:
             self.p.kill()
         self.f.flush()
         self.f.seek(0)
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.f.read().splitlines():
             c = [x.strip() for x in line.split(",")]
@@ -100,6 +100,10 @@ class ClockSampler:
                 mx.append(float(c[1]))
             except ValueError:
                 continue
+            try:
+                pw.append(float(c[2]))
+            except ValueError:
+                pass
             for n, v in zip(names, c[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
@@ -107,6 +111,9 @@ class ClockSampler:
         if sm:
             sm.sort()
             out = {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+            if pw:   # board power under load: with sw_power_cap active the step time is the step's energy over the cap
+                pw.sort()
+                out["power_w"] = pw[len(pw) // 2]
         return out
 
 
