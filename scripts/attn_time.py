@@ -21,9 +21,20 @@ for _ in range(3):
     f()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+n = int(os.environ.get("ATTN_ITERS", "20"))
 e0.record()
-for _ in range(20):
+for _ in range(n):
     f()
 e1.record()
+if n >= 1000:   # long enough to sample the SM clock and board power under sustained load
+    import pynvml
+    pynvml.nvmlInit()
+    h = pynvml.nvmlDeviceGetHandleByIndex(0)
+    cs, ps = [], []
+    while not e1.query():
+        cs.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+        ps.append(pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0)
+    cs, ps = sorted(cs[len(cs) // 3:]), sorted(ps[len(ps) // 3:])
+    print("sustained: sm %d MHz, %.0f W" % (cs[len(cs) // 2], ps[len(ps) // 2]))
 torch.cuda.synchronize()
-print("attention ntok=%d %.1f us  (%s)" % (ntok, e0.elapsed_time(e1) * 50, os.environ.get("VDA_LIB", "in-tree library")))
+print("attention ntok=%d %.1f us  (%s)" % (ntok, e0.elapsed_time(e1) * 1e3 / n, os.environ.get("VDA_LIB", "in-tree library")))
