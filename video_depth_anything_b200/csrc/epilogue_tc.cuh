@@ -117,8 +117,35 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
     }
   }
   // ---------------------------------------------------------------- phase 1
+  constexpr bool LEAN = (EK == EK_STORE || EK == EK_GELU) && !GEGLU;
+  if constexpr (LEAN) {
+    // Both 32-column halves are requested from TMEM before the first wait: one round trip per chunk instead of two (the
+    // GELU kind's epilogue is its GEMM's critical path; registers are not short here).
+    float v[2][32];
+    ptx::tmem_ld32(tcol, v[0]);
+    ptx::tmem_ld32(tcol + 32, v[1]);
+    ptx::tmem_ld_wait();
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
+    for (int h = 0; h < 2; ++h) {
+      const float* bv = sbias + c + h * 32;
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        const float4 b4 = *reinterpret_cast<const float4*>(bv + i);
+        v[h][i] += b4.x; v[h][i + 1] += b4.y; v[h][i + 2] += b4.z; v[h][i + 3] += b4.w;
+      }
+      if constexpr (EK == EK_GELU) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {  // fc1's output is a bf16 tensor: round (paired convert), then GELU
+          const uint32_t r = pack_bf16x2(v[h][i], v[h][i + 1]);
+          gelu_fast2(bf16lo_to_f32(r), bf16hi_to_f32(r), v[h][i], v[h][i + 1]);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) pk[h * 16 + (i >> 1)] = pack_bf16x2(v[h][i], v[h][i + 1]);
+    }
+  }
+#pragma unroll
+  for (int h = 0; h < (LEAN ? 0 : 2); ++h) {
     float v[32];
     if constexpr (GEGLU) {
       float g[32];
@@ -227,6 +254,27 @@ __device__ __forceinline__ void epi_chunk_tc(const Epi& e, const RowIdx& ri, int
                    "f"(__fmul_rn(bf16hi_to_f32(p.x), g4.y)), "f"(__fmul_rn(bf16lo_to_f32(p.y), g4.z)),
                    "f"(__fmul_rn(bf16hi_to_f32(p.y), g4.w))
                    : "memory");
+    }
+    __syncwarp();  // the tile is rewritten by the next chunk
+    return;
+  }
+  if constexpr (EK == EK_STORE || EK == EK_GELU || EK == EK_GEGLU) {
+    // Nothing to add: the staged bf16 is the output.  All eight row-index shuffles and all eight 16-byte shared-memory
+    // loads go out before the first store, and the stores are predicated instead of branched around: the loop form
+    // (shuffle -> compare -> branch -> load -> address -> store, eight times in a row) was a chain of ~100 clk per
+    // iteration and 37 % of the GELU kind's epilogue, which is that GEMM's critical path (profiles/ncu_gemm_gelu8_r02c.txt).
+    uint4 pp[8];
+    int orow[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      const int rr = 4 * t + (lane >> 3);
+      pp[t] = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((j ^ (rr & 7)) << 4));
+      orow[t] = __shfl_sync(0xffffffffu, ri.out_row, rr);
+    }
+    bf16* obase = reinterpret_cast<bf16*>(e.out) + ocol;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      if (orow[t] >= 0 && col_ok) *reinterpret_cast<uint4*>(obase + (long long)(orow[t] + row_add) * e.ldo) = pp[t];
     }
     __syncwarp();  // the tile is rewritten by the next chunk
     return;

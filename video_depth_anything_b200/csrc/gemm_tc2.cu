@@ -15,6 +15,13 @@
 #include "ptx.cuh"
 #include "tmap.h"
 
+#ifdef TC2_TRACE  // epilogue timeline of CTA 0, epilogue warp 0 (scripts/gemm_trace.py); debugging aid
+__device__ long long g_tc2_trace[64 * 4];
+extern "C" int vda_debug_tc2_trace(long long* out) { return (int)cudaMemcpyFromSymbol(out, g_tc2_trace, sizeof(g_tc2_trace)); }
+#define TC2_T(ev) do { if (blockIdx.x == 0 && ew == 0 && lane == 0 && tcount < 64) g_tc2_trace[tcount * 4 + (ev)] = clock64(); } while (0)
+#else
+#define TC2_T(ev)
+#endif
 namespace {
 
 constexpr int BM = 128, BK = 64, BN = 256;  // per-CTA accumulator: 128 x 256; pair tile 256 x 256
@@ -39,6 +46,7 @@ struct Tc2Args {
   int taps, ksplit, m_padded, gb, gh, gw;
   int tiles_m, tiles_n;  // pair tiles (256 x 256)
 };
+
 
 template <int EK>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PairCfg<EK>::NUM_THREADS, 1)
@@ -170,16 +178,29 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     float* sbias_all = reinterpret_cast<float*>(epi_smem + NUM_EPI_WARPS * 4096);
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+    [[maybe_unused]] int tcount = 0;
+    // One bias column per epilogue thread (BN = 256 = 8 warps x 32), fetched one tile AHEAD: the global load's round trip
+    // sits under the previous tile's epilogue instead of between the tiles -- the GELU kind is epilogue-bound (8.4 k clk
+    // of epilogue per 8.0 k clk of MMAs per tile, scripts/gemm_trace.py), so what happens between two tiles is on its
+    // critical path.
+    static_assert(NUM_EPI_WARPS * 32 == BN, "one bias column per epilogue thread");
+    auto bias_of = [&](int tile_) {
+      const int n = (tile_ % a.tiles_n) * BN + et;
+      return (tile_ < num_tiles && e.bias != nullptr && n < a.N) ? epi_bias(e, n) : 0.f;
+    };
+    float bias_next = bias_of(pair);
+    for (int tile = pair; tile < num_tiles; tile += num_pairs, ++tcount) {
       const int m0 = (tile / a.tiles_n) * (2 * BM) + (int)rank * BM, n0 = (tile % a.tiles_n) * BN;
       float* sbias = sbias_all + acc * BN;
-      for (int i = et; i < BN; i += NUM_EPI_WARPS * 32) {
-        const int n = n0 + i;
-        sbias[i] = (e.bias != nullptr && n < a.N) ? epi_bias(e, n) : 0.f;
-      }
+      sbias[et] = bias_next;
+      // (reading the bias straight from global memory instead, to drop this CTA-wide barrier, made the GELU epilogue
+      // slower: 9.2 k against 8.3 k clk per tile -- generic 16-byte loads in place of shared-memory ones)
       asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
+      bias_next = bias_of(tile + num_pairs);
+      TC2_T(0);
       ptx::mbar_wait(&tfull[acc], acc_phase);
       ptx::tc_fence_after();
+      TC2_T(1);
       const int m = m0 + q * 32 + lane;
       const RowIdx ri = make_row_idx(e, m);
       const uint32_t trow = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
@@ -206,6 +227,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
       ptx::tc_fence_before();
       __syncwarp();
+      TC2_T(2);
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty[acc]), 0));
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
