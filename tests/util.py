@@ -57,11 +57,8 @@ def bf16_gate(name, ours, ref_bf16, ref_f32, mean_factor=1.5):
                                       not chaotic (trained-like weights); 1.5 with the random recipe, whose 12 / 24 blocks
                                       amplify each run's per-block rounding error (equal to the reference's, stage by stage:
                                       tests/test_gpu_parity.py) by a factor that varies from input to input
-      (b) agreement: err(ours, ref_bf16) <= max(1e-2, 3 x err(ref_bf16, fp32)) at the max -- the triangle inequality over
-          (a)'s bound and the reference's own deviation: |ours - ref_bf16| <= |ours - fp32| + |ref_bf16 - fp32|; the worst
-          pixel of two independent bf16 evaluations need not be the same pixel, so no tighter max follows from (a) (a
-          28x42 case sat at 2.5 x with equal means); AbsRel <= max(1e-3, 2 x) -- on average two independent bf16
-          evaluations differ by about sqrt(2) x the deviation of either from the fp32 result
+      (b) agreement: err(ours, ref_bf16) <= max(1e-2, 2 x err(ref_bf16, fp32)) at the max; AbsRel <= max(1e-3, 2 x) -- two
+          independent bf16 evaluations differ by about sqrt(2) x the deviation of either from the fp32 result
     Rounding-point fidelity itself is pinned stage by stage with teacher-forced inputs (tests/test_gpu_parity.py) and kernel
     by kernel (test_gpu_kernels.py / test_gpu_tc.py, <= 2 bf16 ulps)."""
     e_ref, e_ours, e_x = rel_err_map(ref_bf16, ref_f32), rel_err_map(ours, ref_f32), rel_err_map(ours, ref_bf16)
@@ -75,6 +72,6 @@ def bf16_gate(name, ours, ref_bf16, ref_f32, mean_factor=1.5):
     assert np.isfinite(r["x_max"]) and np.isfinite(r["ours_max"]), name
     assert r["ours_max"] <= max(1e-2, 2.0 * r["ref_max"]), (name, r)
     assert r["ours_mean"] <= max(1e-3, mean_factor * r["ref_mean"]), (name, r)
-    assert r["x_max"] <= max(1e-2, 3.0 * r["ref_max"]), (name, r)
+    assert r["x_max"] <= max(1e-2, 2.0 * r["ref_max"]), (name, r)
     assert ar_x <= max(1e-3, 2.0 * ar_ref), (name, r)
     return r

@@ -263,7 +263,7 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
         // row sum run as packed fp32 pairs (FFMA2 / FADD2: one issue slot for two).  Moving 2 / 4 / 6 of the 32 pairs' exp2
         // onto the FMA pipe (Cody-Waite + cubic, +5 issue slots per element) measured 376 / 390 / 435 us against 376:
         // both resources are at their balance point, so the MUFU stays the exponential's unit.
-        uint64_t ps0 = pk2(0.f, 0.f), ps1 = pk2(0.f, 0.f);
+        uint64_t ps = pk2(0.f, 0.f);  // (sum over the even keys, sum over the odd keys), each in key order
         const uint64_t c2 = pk2(C2, C2), nmb = pk2(-mb, -mb);
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
@@ -271,12 +271,11 @@ flash_attn_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ 
           float x0, x1;
           upk2(x, x0, x1);
           const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
-          if (i & 1) ps1 = add2(ps1, pk2(p0, p1));
-          else ps0 = add2(ps0, pk2(p0, p1));
+          ps = add2(ps, pk2(p0, p1));
           sp[i] = pack_bf16x2(p0, p1);
         }
         float psum0, psum1;
-        upk2(add2(ps0, ps1), psum0, psum1);
+        upk2(ps, psum0, psum1);
         l = fmaf(l, alpha, psum0 + psum1);  // row sum over this stream's keys; the halves are merged at the end
         FA_T(4);
         // ---- PV(j-1) must be complete before P (smem) is overwritten or O (TMEM) is rescaled
