@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Epilogue timeline of the pair GEMM (needs a library built with -DTC2_TRACE; debugging aid): per tile of CTA 0, how long
 epilogue warp 0 waited for the accumulator and how long its share of the epilogue took.
-VDA_LIB=scripts/micro/libvda_tc2trace.so python scripts/gemm_trace.py [gelu|store|resid]"""
+VDA_LIB=scripts/micro/libvda_tc2trace.so python scripts/gemm_trace.py [gelu|store|resid|store4096]"""
 import ctypes as C
 import os
 import sys
@@ -16,7 +16,8 @@ if os.environ.get("VDA_LIB"):
 lib = L.load()
 dev = "cuda"
 kind = sys.argv[1] if len(sys.argv) > 1 else "gelu"
-M, N, K = 43840, (1024 if kind == "resid" else 4096), (4096 if kind == "resid" else 1024)
+deep = kind in ("resid", "store4096")   # fc2's shape (N = 1024, K = 4096) instead of fc1's
+M, N, K = 43840, (1024 if deep else 4096), (4096 if deep else 1024)
 A = torch.randn(M, K, device=dev).bfloat16()
 B = (torch.randn(N, K, device=dev) / K ** 0.5).bfloat16()
 bias = torch.randn(N, device=dev)
